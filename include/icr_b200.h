@@ -1,0 +1,150 @@
+/* icr_b200.h -- C ABI of the B200-native compression-reward path (libicr_b200.so).
+ *
+ * Drop-in boundary for ONE hot path of moritzschramm/image-compression-cpp:
+ *   segment_stats -> masked slice -> png_size_estimator -> compute_rewards.
+ * Plain pointers and sizes only; no torch types.  Every device pointer must belong to the
+ * device the workspace was created on; every call is asynchronous on `stream` unless noted.
+ * All entry points return 0 on success and a non-zero ICR_E* code otherwise; the message of
+ * the last failure on the calling thread is icr_last_error().  (The reference reports errors
+ * as C++ exceptions: TORCH_CHECK / std::runtime_error, src/compute_rewards.cu:70-75,
+ * src/png_size_estimator.cu:483-484; the C++ shim in host/ maps codes back to those.)
+ *
+ * Citations are relative to the reference checkout (/root/reference).
+ */
+#ifndef ICR_B200_H
+#define ICR_B200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ICR_OK 0
+#define ICR_EINVAL 1      /* bad argument (null pointer, bad shape, channels outside 1..4) */
+#define ICR_ECUDA 2       /* CUDA runtime error */
+#define ICR_ECAPACITY 3   /* workspace too small for this call */
+#define ICR_EDATA 4       /* data-dependent failure reported by icr_check (label range, K > Kmax) */
+
+#define ICR_LABELS_I32 0  /* what rama_torch_batched hands over: src/rama_wrapper.cu:99 */
+#define ICR_LABELS_I64 1  /* what compute_rewards_batched converts to: src/compute_rewards.cu:97 */
+
+typedef void* icr_stream;               /* a cudaStream_t */
+typedef struct icr_workspace icr_workspace;
+
+/* The eight estimator/reward knobs: default arguments of include/compute_rewards.cuh:9-16. */
+typedef struct {
+    int32_t min_pixels;      /* 1 */
+    int32_t L_min;           /* 4 */
+    float beta;              /* 0.012167f */
+    float b_match_token;     /* 18.0f */
+    float gamma;             /* 0.1f */
+    double overhead_base;    /* 9.308622 */
+    int32_t adaptive_filter; /* 1 */
+    double lambda;           /* 0.5 */
+} icr_params;
+
+const char* icr_last_error(void);
+int icr_version(void);
+void icr_default_params(icr_params* p);
+
+/* ---- workspace: replaces the hidden thread_local PngEstimatorWorkspace
+ * (include/png_size_estimator.cuh:12-58, src/png_size_estimator.cu:466-469) and the per-image
+ * at::empty calls of src/compute_rewards.cu:143-149.  V = B*S label maps of HxW pixels with at
+ * most Kmax segments each.  Grow-only is the caller's business: create one per (thread, device,
+ * shape). */
+size_t icr_workspace_bytes(int V, int H, int W, int Kmax);
+int icr_workspace_create(icr_workspace** ws, int device, int V, int H, int W, int Kmax);
+int icr_workspace_destroy(icr_workspace* ws);
+
+/* ---- the batch entry: compute_rewards_batched, src/compute_rewards.cu:55-196.
+ * images  f32 [B,3,H,W] device, planar, byte values 0..255 (Rule C applied inside)
+ * labels  [B,S,H,W] device, int32 or int64, any values whose per-map spread (max-min) is below
+ *         the bitmap capacity icr_label_capacity(H,W); S label maps share one image (S=1 is the
+ *         reference's call; S>1 equals images.repeat_interleave(S,0))
+ * image_sizes f64 [B] device;  rewards f64 [B*S] device (out)
+ * Asynchronous: no host synchronisation, no allocation. */
+int icr_compute_rewards(const float* images, const void* labels, int label_dtype,
+                        const double* image_sizes, int B, int S, int H, int W,
+                        const icr_params* params, double* rewards,
+                        icr_workspace* ws, icr_stream stream);
+
+/* Same through HOST buffers (pinned or pageable): H2D of images/labels/sizes, the path, D2H of
+ * rewards, then a stream synchronise.  This is the call bench.py times as `e2e`. */
+int icr_compute_rewards_host(const float* images_h, const void* labels_h, int label_dtype,
+                             const double* image_sizes_h, int B, int S, int H, int W,
+                             const icr_params* params, double* rewards_h,
+                             icr_workspace* ws, icr_stream stream);
+
+/* Synchronises `stream` and reports data-dependent failures of the calls issued so far on this
+ * workspace: returns ICR_EDATA (and the first offending label map in *first_bad, may be NULL)
+ * if a label map's value spread exceeded the capacity or its K exceeded Kmax; rewards of such
+ * maps are NaN.  The reference has the same one-sync-per-call behaviour, only 2 per image. */
+int icr_check(icr_workspace* ws, icr_stream stream, int* first_bad);
+int64_t icr_label_capacity(int H, int W);
+
+/* ---- segment_stats batched, with Rule L folded in (src/compute_rewards.cu:131-141 +
+ * src/segment_stats.cu:11-77).  Fills the workspace tables and, when non-NULL, copies them out:
+ * K_out int32 [V]; counts int32 [V,Kmax]; bboxes int32 [V,Kmax,4] = (x0,y0,x1,y1) inclusive. */
+int icr_segment_stats(const void* labels, int label_dtype, int V, int H, int W,
+                      int32_t* K_out, int32_t* counts, int32_t* bboxes,
+                      icr_workspace* ws, icr_stream stream);
+
+/* Pointer-level drop-in for compute_counts_bboxes_from_compact_labels_cuda
+ * (include/segment_stats.cuh:6-10): compact int64 labels [H,W] with values 0..K-1. */
+int icr_counts_bboxes_from_compact_labels(const int64_t* labels_hw, int H, int W, int K,
+                                          int32_t* counts_k, int32_t* bboxes_k4, icr_stream stream);
+
+/* Pointer-level drop-in for estimate_png_size_masked_segment_to_output
+ * (include/png_size_estimator.cuh:61-71): one segment, image u8 [H,W,channels], compact int64
+ * labels, writes one double to out_dev.  w<=0 or h<=0 writes 0.0 (src/png_size_estimator.cu:485-488).
+ * dbg_* (device, may be NULL): row costs u32 [h*5], filter ids u8 [h], histogram u32 [channels*256],
+ * match triple u64 [3] -- tables the reference keeps private in its workspace. */
+int icr_estimate_png_size_segment(const uint8_t* img_hwc_u8, int full_W, int full_H, int channels,
+                                  const int64_t* labels_compact_hw, const int32_t* counts_k,
+                                  int64_t seg_id_k, int x0, int y0, int w, int h,
+                                  int32_t min_pixels, int L_min, float beta, float b_match_token,
+                                  float gamma, double overhead_base, int adaptive_filter,
+                                  double* out_dev,
+                                  uint32_t* dbg_row_costs, uint8_t* dbg_filter_id,
+                                  uint32_t* dbg_hist, unsigned long long* dbg_match,
+                                  icr_stream stream);
+
+/* ---- read-back of the tables the last icr_compute_rewards / icr_segment_stats left in the
+ * workspace (device pointers, valid until the next call): K int32 [V], counts int32 [V,Kmax],
+ * bboxes int32 [V,Kmax,4], seg_sizes f64 [V,Kmax], pixlab u32 [V,H,W,2] = (RGBA bytes, compact id). */
+int icr_workspace_tables(icr_workspace* ws, const int32_t** K, const int32_t** counts,
+                         const int32_t** bboxes, const double** seg_sizes, const uint32_t** pixlab,
+                         int* Kmax);
+
+/* Debug tables of ONE segment of the batch path (label map v, compact id k), produced by the
+ * same device code the batch uses: row costs u32 [h*5], filter ids u8 [h], histogram u32 [4*256],
+ * match u64 [3] (device pointers, may be NULL). */
+int icr_debug_segment(icr_workspace* ws, int v, int k, const icr_params* params,
+                      uint32_t* row_costs, uint8_t* filter_id, uint32_t* hist,
+                      unsigned long long* match, double* size_out, icr_stream stream);
+
+/* Masked slice of segment k of label map v (Rule P; src/image_slicer.cpp:48-74): u8 [h,w,4]. */
+int icr_slice_segment(icr_workspace* ws, int v, int k, uint8_t* out_hw4, size_t out_capacity,
+                      icr_stream stream);
+
+/* ---- Rule E + advantage (include/ema_baseline.hpp:11-21, src/fcn/training.cpp:178-181).
+ * state (device, 2 doubles): {value, initialized flag}.  sum_count (device, 2 doubles) holds the
+ * global {sum of rewards, count} -- after an all-reduce when the batch is sharded; pass NULL to
+ * have it computed from rewards[0..n).  advantages (device, may be NULL) f64 [n]: (r - value)
+ * standardised with the population std clamped at 1e-6. */
+int icr_ema_update(const double* rewards, int n, const double* sum_count, double momentum,
+                   double* state, double* advantages, icr_stream stream);
+int icr_reward_sum_count(const double* rewards, int n, double* sum_count, icr_stream stream);
+
+/* Exhaustive device self-test of the packed-byte filter arithmetic against scalar code
+ * (all 2^24 Paeth triples, all Avg pairs, all cost bytes): *mismatches is a host int. Synchronous. */
+int icr_selftest(int* mismatches);
+
+/* Number of kernels this library launched on the calling thread since the last reset. */
+long long icr_launch_count(int reset);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
