@@ -1,0 +1,306 @@
+// C ABI of libicr_b200.so (include/icr_b200.h): workspace, argument checks, launch sequencing.
+// No torch, no allocation and no host synchronisation inside icr_compute_rewards.
+#include "icr_internal.h"
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+struct icr_workspace {
+    int device, V, H, W, Kmax;
+    char* base;            // one device allocation
+    size_t bytes;
+    icr::Tables t;
+    // device staging for the host-buffer entry
+    float* st_images; void* st_labels; double* st_sizes; double* st_rewards;
+    size_t st_images_bytes, st_labels_bytes;
+};
+
+namespace icr {
+
+static thread_local std::string g_err;
+static thread_local long long g_launches = 0;
+void count_launch(int n) { g_launches += n; }
+
+static int fail(int code, const std::string& msg) { g_err = msg; return code; }
+static int cuda_fail(cudaError_t e, const char* what) {
+    return fail(ICR_ECUDA, std::string("CUDA error in ") + what + ": " + cudaGetErrorString(e));
+}
+#define ICR_CUDA(x, what) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) return cuda_fail(e_, what); } while (0)
+
+static size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
+
+struct Layout { size_t pixlab, K, status, counts, bboxes, sizes, err, big_filter, clog2, total; };
+
+static Layout layout(int V, int H, int W, int Kmax) {
+    Layout l; size_t o = 0;
+    const size_t HW = (size_t)H * W;
+    l.pixlab = o; o = align_up(o + (size_t)V * HW * sizeof(uint2));
+    l.K = o; o = align_up(o + (size_t)V * 4);
+    l.status = o; o = align_up(o + (size_t)V * 4);
+    l.counts = o; o = align_up(o + (size_t)V * Kmax * 4);
+    l.bboxes = o; o = align_up(o + (size_t)V * Kmax * 16);
+    l.sizes = o; o = align_up(o + (size_t)V * Kmax * 8);
+    l.err = o; o = align_up(o + 16);
+    l.big_filter = o; o = align_up(o + (size_t)V * BIG_CTAS * H);
+    l.clog2 = o; o = align_up(o + (size_t)CLOG2_N * 8);
+    l.total = o;
+    return l;
+}
+
+static EstParams widen(const icr_params* p) {
+    EstParams e;
+    e.min_pixels = p->min_pixels; e.L_min = p->L_min; e.adaptive = p->adaptive_filter ? 1 : 0;
+    e.beta = (double)p->beta; e.token = (double)p->b_match_token; e.gamma = (double)p->gamma;   // float -> double as :588
+    e.overhead = p->overhead_base; e.lambda = p->lambda;
+    return e;
+}
+
+static int check_shape(const icr_workspace* ws, int V, int H, int W) {
+    if (!ws) return fail(ICR_EINVAL, "workspace is null");
+    if (V <= 0 || H <= 0 || W <= 0) return fail(ICR_EINVAL, "B, S, H and W must be positive");
+    if (V > ws->V || H != ws->H || W != ws->W)
+        return fail(ICR_ECAPACITY, "workspace was created for V=" + std::to_string(ws->V) + " maps of " + std::to_string(ws->H) +
+                                       "x" + std::to_string(ws->W) + ", call needs V=" + std::to_string(V) + " of " +
+                                       std::to_string(H) + "x" + std::to_string(W));
+    return ICR_OK;
+}
+
+}  // namespace icr
+
+using namespace icr;
+
+extern "C" {
+
+const char* icr_last_error(void) { return g_err.c_str(); }
+int icr_version(void) { return 100; }
+long long icr_launch_count(int reset) { long long n = g_launches; if (reset) g_launches = 0; return n; }
+
+void icr_default_params(icr_params* p) {
+    if (!p) return;
+    p->min_pixels = 1; p->L_min = 4; p->beta = 0.012167f; p->b_match_token = 18.0f; p->gamma = 0.1f;
+    p->overhead_base = 9.308622; p->adaptive_filter = 1; p->lambda = 0.5;
+}
+
+int64_t icr_label_capacity(int H, int W) { return label_capacity(H, W); }
+
+size_t icr_workspace_bytes(int V, int H, int W, int Kmax) {
+    if (V <= 0 || H <= 0 || W <= 0 || Kmax <= 0) return 0;
+    return layout(V, H, W, Kmax).total;
+}
+
+int icr_workspace_create(icr_workspace** out, int device, int V, int H, int W, int Kmax) {
+    if (!out) return fail(ICR_EINVAL, "null workspace out-pointer");
+    *out = nullptr;
+    if (V <= 0 || H <= 0 || W <= 0 || Kmax <= 0) return fail(ICR_EINVAL, "V, H, W and Kmax must be positive");
+    if ((int64_t)H * W > LCAP_MAX)
+        return fail(ICR_ECAPACITY, "label maps above " + std::to_string(LCAP_MAX) + " pixels are not supported yet (shared-memory bitmap)");
+    if ((int64_t)Kmax > (int64_t)H * W) Kmax = H * W;
+    ICR_CUDA(cudaSetDevice(device), "cudaSetDevice");
+    icr_workspace* ws = new icr_workspace();
+    std::memset(ws, 0, sizeof *ws);
+    ws->device = device; ws->V = V; ws->H = H; ws->W = W; ws->Kmax = Kmax;
+    const Layout l = layout(V, H, W, Kmax);
+    ws->bytes = l.total;
+    cudaError_t e = cudaMalloc((void**)&ws->base, l.total);
+    if (e != cudaSuccess) { delete ws; return cuda_fail(e, "cudaMalloc(workspace)"); }
+    Tables& t = ws->t;
+    t.pixlab = (uint2*)(ws->base + l.pixlab); t.K = (int32_t*)(ws->base + l.K); t.status = (int32_t*)(ws->base + l.status);
+    t.counts = (int32_t*)(ws->base + l.counts); t.bboxes = (int4*)(ws->base + l.bboxes); t.seg_sizes = (double*)(ws->base + l.sizes);
+    t.err = (int32_t*)(ws->base + l.err); t.big_filter = (uint8_t*)(ws->base + l.big_filter); t.clog2 = (const double*)(ws->base + l.clog2);
+    t.V = V; t.H = H; t.W = W; t.Kmax = Kmax;
+    std::vector<double> tab(CLOG2_N);
+    tab[0] = 0.0;
+    for (int c = 1; c < CLOG2_N; ++c) tab[c] = (double)c * std::log2((double)c);
+    e = cudaMemcpy(ws->base + l.clog2, tab.data(), CLOG2_N * 8, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemset(ws->base + l.K, 0, (size_t)V * 4);
+    if (e == cudaSuccess) e = cudaMemset(ws->base + l.status, 0, (size_t)V * 4);
+    if (e == cudaSuccess) e = cudaMemset(ws->base + l.err, 0, 16);
+    if (e != cudaSuccess) { cudaFree(ws->base); delete ws; return cuda_fail(e, "workspace init"); }
+    *out = ws;
+    return ICR_OK;
+}
+
+int icr_workspace_destroy(icr_workspace* ws) {
+    if (!ws) return ICR_OK;
+    cudaSetDevice(ws->device);
+    cudaFree(ws->base);
+    cudaFree(ws->st_images); cudaFree(ws->st_labels); cudaFree(ws->st_sizes); cudaFree(ws->st_rewards);
+    delete ws;
+    return ICR_OK;
+}
+
+int icr_compute_rewards(const float* images, const void* labels, int label_dtype, const double* image_sizes,
+                        int B, int S, int H, int W, const icr_params* params, double* rewards,
+                        icr_workspace* ws, icr_stream stream) {
+    if (!images || !labels || !image_sizes || !rewards || !params) return fail(ICR_EINVAL, "null ptr");
+    if (label_dtype != ICR_LABELS_I32 && label_dtype != ICR_LABELS_I64) return fail(ICR_EINVAL, "labels must be int32 or int64");
+    if (B <= 0 || S <= 0) return fail(ICR_EINVAL, "B and S must be positive");
+    if (int rc = check_shape(ws, B * S, H, W)) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    Tables t = ws->t;
+    t.V = B * S;
+    const EstParams p = widen(params);
+    ICR_CUDA(launch_prep(images, labels, label_dtype, B, S, t, true, st), "prep");
+    ICR_CUDA(launch_estimate(t, p, st), "estimate");
+    ICR_CUDA(launch_big(t, p, st), "big_segment");
+    ICR_CUDA(launch_reward(t, p, image_sizes, S, rewards, st), "reward");
+    return ICR_OK;
+}
+
+int icr_compute_rewards_host(const float* images_h, const void* labels_h, int label_dtype, const double* image_sizes_h,
+                             int B, int S, int H, int W, const icr_params* params, double* rewards_h,
+                             icr_workspace* ws, icr_stream stream) {
+    if (!images_h || !labels_h || !image_sizes_h || !rewards_h || !params) return fail(ICR_EINVAL, "null ptr");
+    if (label_dtype != ICR_LABELS_I32 && label_dtype != ICR_LABELS_I64) return fail(ICR_EINVAL, "labels must be int32 or int64");
+    if (B <= 0 || S <= 0) return fail(ICR_EINVAL, "B and S must be positive");
+    if (int rc = check_shape(ws, B * S, H, W)) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t HW = (size_t)H * W;
+    const size_t ib = (size_t)B * 3 * HW * 4, lb = (size_t)B * S * HW * (label_dtype == ICR_LABELS_I64 ? 8 : 4);
+    if (ws->st_images_bytes < ib) {
+        cudaFree(ws->st_images); ws->st_images = nullptr; ws->st_images_bytes = 0;
+        ICR_CUDA(cudaMalloc((void**)&ws->st_images, ib), "cudaMalloc(staging images)");
+        ws->st_images_bytes = ib;
+    }
+    if (ws->st_labels_bytes < lb) {
+        cudaFree(ws->st_labels); ws->st_labels = nullptr; ws->st_labels_bytes = 0;
+        ICR_CUDA(cudaMalloc(&ws->st_labels, lb), "cudaMalloc(staging labels)");
+        ws->st_labels_bytes = lb;
+    }
+    if (!ws->st_sizes) {
+        ICR_CUDA(cudaMalloc((void**)&ws->st_sizes, (size_t)ws->V * 8), "cudaMalloc(staging sizes)");
+        ICR_CUDA(cudaMalloc((void**)&ws->st_rewards, (size_t)ws->V * 8), "cudaMalloc(staging rewards)");
+    }
+    ICR_CUDA(cudaMemcpyAsync(ws->st_images, images_h, ib, cudaMemcpyHostToDevice, st), "H2D images");
+    ICR_CUDA(cudaMemcpyAsync(ws->st_labels, labels_h, lb, cudaMemcpyHostToDevice, st), "H2D labels");
+    ICR_CUDA(cudaMemcpyAsync(ws->st_sizes, image_sizes_h, (size_t)B * 8, cudaMemcpyHostToDevice, st), "H2D sizes");
+    if (int rc = icr_compute_rewards(ws->st_images, ws->st_labels, label_dtype, ws->st_sizes, B, S, H, W, params,
+                                     ws->st_rewards, ws, stream)) return rc;
+    ICR_CUDA(cudaMemcpyAsync(rewards_h, ws->st_rewards, (size_t)B * S * 8, cudaMemcpyDeviceToHost, st), "D2H rewards");
+    ICR_CUDA(cudaStreamSynchronize(st), "stream sync");
+    return ICR_OK;
+}
+
+int icr_check(icr_workspace* ws, icr_stream stream, int* first_bad) {
+    if (!ws) return fail(ICR_EINVAL, "workspace is null");
+    int32_t h[2] = {0, 0};
+    ICR_CUDA(cudaMemcpyAsync(h, ws->t.err, 8, cudaMemcpyDeviceToHost, (cudaStream_t)stream), "D2H error flag");
+    ICR_CUDA(cudaStreamSynchronize((cudaStream_t)stream), "stream sync");
+    if (first_bad) *first_bad = h[0] ? 0x7fffffff - h[1] : -1;
+    if (!h[0]) return ICR_OK;
+    ICR_CUDA(cudaMemsetAsync(ws->t.err, 0, 8, (cudaStream_t)stream), "reset error flag");
+    return fail(ICR_EDATA, "label map " + std::to_string(0x7fffffff - h[1]) +
+                               ": label spread exceeds icr_label_capacity(H,W) or segment count exceeds Kmax; its reward is NaN");
+}
+
+int icr_segment_stats(const void* labels, int label_dtype, int V, int H, int W, int32_t* K_out, int32_t* counts,
+                      int32_t* bboxes, icr_workspace* ws, icr_stream stream) {
+    if (!labels) return fail(ICR_EINVAL, "null ptr");
+    if (label_dtype != ICR_LABELS_I32 && label_dtype != ICR_LABELS_I64) return fail(ICR_EINVAL, "labels must be int32 or int64");
+    if (int rc = check_shape(ws, V, H, W)) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    Tables t = ws->t;
+    t.V = V;
+    ICR_CUDA(launch_prep(nullptr, labels, label_dtype, V, 1, t, false, st), "prep");
+    if (K_out) ICR_CUDA(cudaMemcpyAsync(K_out, t.K, (size_t)V * 4, cudaMemcpyDeviceToDevice, st), "copy K");
+    if (counts) ICR_CUDA(cudaMemcpyAsync(counts, t.counts, (size_t)V * t.Kmax * 4, cudaMemcpyDeviceToDevice, st), "copy counts");
+    if (bboxes) ICR_CUDA(cudaMemcpyAsync(bboxes, t.bboxes, (size_t)V * t.Kmax * 16, cudaMemcpyDeviceToDevice, st), "copy bboxes");
+    return ICR_OK;
+}
+
+int icr_counts_bboxes_from_compact_labels(const int64_t* labels_hw, int H, int W, int K, int32_t* counts_k,
+                                          int32_t* bboxes_k4, icr_stream stream) {
+    if (!labels_hw || !counts_k || !bboxes_k4) return fail(ICR_EINVAL, "null ptr");
+    if (H <= 0 || W <= 0 || K < 0) return fail(ICR_EINVAL, "bad shape");
+    ICR_CUDA(launch_compact_stats(labels_hw, H, W, K, counts_k, bboxes_k4, (cudaStream_t)stream), "compact stats");
+    return ICR_OK;
+}
+
+int icr_estimate_png_size_segment(const uint8_t* img, int full_W, int full_H, int channels, const int64_t* labels,
+                                  const int32_t* counts_k, int64_t seg_id_k, int x0, int y0, int w, int h,
+                                  int32_t min_pixels, int L_min, float beta, float b_match_token, float gamma,
+                                  double overhead_base, int adaptive_filter, double* out_dev, uint32_t* dbg_row_costs,
+                                  uint8_t* dbg_filter_id, uint32_t* dbg_hist, unsigned long long* dbg_match,
+                                  icr_stream stream) {
+    if (!img || !labels || !counts_k || !out_dev) return fail(ICR_EINVAL, "null ptr");                 // :483
+    if (channels < 1 || channels > 4) return fail(ICR_EINVAL, "channels must be 1..4");                // :484
+    cudaStream_t st = (cudaStream_t)stream;
+    if (w <= 0 || h <= 0) {                                                                             // :485-488
+        ICR_CUDA(cudaMemsetAsync(out_dev, 0, sizeof(double), st), "memset out");
+        return ICR_OK;
+    }
+    if (x0 < 0 || y0 < 0 || x0 + w > full_W || y0 + h > full_H) return fail(ICR_EINVAL, "bbox outside the image");
+    icr_params prm{min_pixels, L_min, beta, b_match_token, gamma, overhead_base, adaptive_filter, 0.0};
+    // per-(thread, device) grow-only filter-id scratch, like the reference's hidden workspace (:466-469)
+    static thread_local uint8_t* scratch[16] = {nullptr};
+    static thread_local int scratch_cap[16] = {0};
+    int dev = 0;
+    ICR_CUDA(cudaGetDevice(&dev), "cudaGetDevice");
+    if (dev < 0 || dev >= 16) return fail(ICR_EINVAL, "device index above 15");
+    if (scratch_cap[dev] < h) {
+        if (scratch[dev]) { ICR_CUDA(cudaStreamSynchronize(st), "sync before scratch growth"); cudaFree(scratch[dev]); }
+        scratch[dev] = nullptr; scratch_cap[dev] = 0;
+        ICR_CUDA(cudaMalloc((void**)&scratch[dev], (size_t)h), "cudaMalloc(filter scratch)");
+        scratch_cap[dev] = h;
+    }
+    ICR_CUDA(launch_single_segment(img, full_W, full_H, channels, labels, seg_id_k, x0, y0, w, h, widen(&prm), out_dev,
+                                   dbg_row_costs, dbg_filter_id, dbg_hist, dbg_match, scratch[dev], st), "single segment");
+    return ICR_OK;
+}
+
+int icr_workspace_tables(icr_workspace* ws, const int32_t** K, const int32_t** counts, const int32_t** bboxes,
+                         const double** seg_sizes, const uint32_t** pixlab, int* Kmax) {
+    if (!ws) return fail(ICR_EINVAL, "workspace is null");
+    if (K) *K = ws->t.K;
+    if (counts) *counts = ws->t.counts;
+    if (bboxes) *bboxes = (const int32_t*)ws->t.bboxes;
+    if (seg_sizes) *seg_sizes = ws->t.seg_sizes;
+    if (pixlab) *pixlab = (const uint32_t*)ws->t.pixlab;
+    if (Kmax) *Kmax = ws->t.Kmax;
+    return ICR_OK;
+}
+
+int icr_debug_segment(icr_workspace* ws, int v, int k, const icr_params* params, uint32_t* row_costs,
+                      uint8_t* filter_id, uint32_t* hist, unsigned long long* match, double* size_out,
+                      icr_stream stream) {
+    if (!ws || !params) return fail(ICR_EINVAL, "null ptr");
+    if (v < 0 || v >= ws->V || k < 0 || k >= ws->Kmax) return fail(ICR_EINVAL, "segment index out of range");
+    const EstParams p = widen(params);
+    cudaStream_t st = (cudaStream_t)stream;
+    // both kernels test the Rule M size criterion on the device; exactly one of them acts
+    ICR_CUDA(launch_estimate_debug(ws->t, p, v, k, row_costs, filter_id, hist, match, size_out, st), "estimate debug");
+    ICR_CUDA(launch_big_debug(ws->t, p, v, k, row_costs, filter_id, hist, match, size_out, st), "big debug");
+    return ICR_OK;
+}
+
+int icr_slice_segment(icr_workspace* ws, int v, int k, uint8_t* out_hw4, size_t out_capacity, icr_stream stream) {
+    if (!ws || !out_hw4) return fail(ICR_EINVAL, "null ptr");
+    if (v < 0 || v >= ws->V || k < 0 || k >= ws->Kmax) return fail(ICR_EINVAL, "segment index out of range");
+    ICR_CUDA(launch_slice(ws->t, v, k, out_hw4, out_capacity, (cudaStream_t)stream), "slice");
+    return ICR_OK;
+}
+
+int icr_ema_update(const double* rewards, int n, const double* sum_count, double momentum, double* state,
+                   double* advantages, icr_stream stream) {
+    if (!rewards || !state) return fail(ICR_EINVAL, "null ptr");
+    if (n <= 0) return fail(ICR_EINVAL, "n must be positive");
+    ICR_CUDA(launch_ema(rewards, n, sum_count, momentum, state, advantages, (cudaStream_t)stream), "ema");
+    return ICR_OK;
+}
+
+int icr_reward_sum_count(const double* rewards, int n, double* sum_count, icr_stream stream) {
+    if (!rewards || !sum_count) return fail(ICR_EINVAL, "null ptr");
+    if (n <= 0) return fail(ICR_EINVAL, "n must be positive");
+    ICR_CUDA(launch_sum_count(rewards, n, sum_count, (cudaStream_t)stream), "sum_count");
+    return ICR_OK;
+}
+
+int icr_selftest(int* mismatches) {
+    if (!mismatches) return fail(ICR_EINVAL, "null ptr");
+    ICR_CUDA(run_selftest(mismatches), "selftest");
+    return ICR_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,222 @@
+// big-segment path: one CTA per segment, any size, any channel count 1..4.
+// Used (a) by the batch for the few segments large enough for Rule M match statistics
+// (chunk = ceil(N/65536) >= L_min, src/png_size_estimator.cu:416-451), and (b) as the
+// pointer-level drop-in for estimate_png_size_masked_segment_to_output (:472-591).
+// Phase 1: a warp per bbox row, lanes along x, packed-byte costs, arg-min -> filter id per row.
+// Phase 2: a thread per reference chunk walks its bytes in stream order, recomputing residuals on
+// the fly (no residual buffer), feeding the shared-memory histogram and the run statistics.
+// Entropy and mean follow the reference's reduction trees (:281-328) exactly.
+#include "icr_internal.h"
+#include "icr_pixel.cuh"
+
+namespace icr {
+
+constexpr int BIG_T = 256;
+
+struct BigDebug { uint32_t* row_costs; uint8_t* filter_id; uint32_t* hist; unsigned long long* match; double* size; };
+
+struct SrcPixlab {          // the batch layout: {RGBA, compact id} per pixel
+    const uint2* base; int W; uint32_t k;
+    __device__ __forceinline__ uint32_t px(int gy, int gx) const {
+        uint2 q = __ldg(base + (int64_t)gy * W + gx);
+        return q.y == k ? q.x : 0u;
+    }
+};
+
+struct SrcRaw {             // the reference's layout: u8 [H,W,C] + compact int64 labels
+    const uint8_t* img; const int64_t* lab; int W, C; int64_t k;
+    __device__ __forceinline__ uint32_t px(int gy, int gx) const {
+        int64_t i = (int64_t)gy * W + gx;
+        if (lab[i] != k) return 0u;
+        uint32_t v = 0;
+        for (int c = 0; c < C; ++c) v |= (uint32_t)img[i * C + c] << (8 * c);
+        return v;
+    }
+};
+
+__device__ __forceinline__ double size_formula_big(double Hbar, unsigned long long ms, unsigned long long mc,
+                                                   unsigned long long mls, unsigned long long N, int h, const EstParams& p) {
+    double f = (N > 0 && ms > 0) ? (double)ms / (double)N : 0.0;
+    double Lbar = mc > 0 ? (double)mls / (double)mc : (double)p.L_min;
+    double b_lit = Hbar + p.beta;
+    double b_match = p.token / Lbar + p.gamma;
+    double b_data = (1.0 - f) * b_lit + f * b_match;
+    return (p.overhead + (double)h) + ((double)N * b_data) / 8.0;
+}
+
+// whole CTA cooperates on one segment; filt = >= h bytes of scratch (global)
+template <class Src>
+__device__ void block_segment(const Src& src, int x0, int y0, int w, int h, int C, const EstParams& p,
+                              uint8_t* filt, double* out, const BigDebug& dbg) {
+    __shared__ uint32_t s_hist[4 * 256];
+    __shared__ double s_red[256];
+    __shared__ double s_Hc[4];
+    __shared__ unsigned long long s_ms, s_mc, s_mls;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+    for (int i = tid; i < 4 * 256; i += BIG_T) s_hist[i] = 0;
+    if (tid == 0) { s_ms = 0; s_mc = 0; s_mls = 0; }
+
+    // ---- phase 1: filter per row (Rule F)
+    for (int y = warp; y < h; y += BIG_T / 32) {
+        int f = 4;
+        if (p.adaptive) {
+            Costs5 c = {0, 0, 0, 0, 0};
+            for (int x = lane; x < w; x += 32) {
+                uint32_t cur = src.px(y0 + y, x0 + x);
+                uint32_t left = x > 0 ? src.px(y0 + y, x0 + x - 1) : 0u;
+                uint32_t up = y > 0 ? src.px(y0 + y - 1, x0 + x) : 0u;
+                uint32_t ul = (x > 0 && y > 0) ? src.px(y0 + y - 1, x0 + x - 1) : 0u;
+                add_costs(c, cur, left, up, ul);
+            }
+            for (int o = 16; o; o >>= 1) {
+                c.none += __shfl_xor_sync(0xffffffffu, c.none, o);
+                c.sub += __shfl_xor_sync(0xffffffffu, c.sub, o);
+                c.up += __shfl_xor_sync(0xffffffffu, c.up, o);
+                c.avg += __shfl_xor_sync(0xffffffffu, c.avg, o);
+                c.paeth += __shfl_xor_sync(0xffffffffu, c.paeth, o);
+            }
+            f = pick_filter(c);
+            if (lane == 0 && dbg.row_costs) {
+                uint32_t* rc = dbg.row_costs + 5 * (int64_t)y;
+                rc[0] = c.none; rc[1] = c.sub; rc[2] = c.up; rc[3] = c.avg; rc[4] = c.paeth;
+            }
+        }
+        if (lane == 0) { filt[y] = (uint8_t)f; if (dbg.filter_id) dbg.filter_id[y] = (uint8_t)f; }
+    }
+    __syncthreads();
+
+    // ---- phase 2: stream walk, one reference chunk per thread step (Rules R, H, M)
+    const unsigned long long N = (unsigned long long)w * h * C;
+    const unsigned long long chunk = (N + 65535ull) / 65536ull;
+    const unsigned long long nchunks = (N + chunk - 1) / chunk;
+    unsigned long long ms = 0, mc = 0;
+    for (unsigned long long t = tid; t < nchunks; t += BIG_T) {
+        const unsigned long long start = t * chunk;
+        const unsigned long long end = min(start + chunk, N);
+        long long pix = -1;
+        uint32_t r4 = 0;
+        int prev = -1, run = 0;
+        for (unsigned long long i = start; i < end; ++i) {
+            const long long pi = (long long)(i / (unsigned)C);
+            const int c = (int)(i - (unsigned long long)pi * C);
+            if (pi != pix) {
+                pix = pi;
+                const int y = (int)(pi / w), x = (int)(pi - (long long)y * w);
+                uint32_t cur = src.px(y0 + y, x0 + x);
+                uint32_t left = x > 0 ? src.px(y0 + y, x0 + x - 1) : 0u;
+                uint32_t up = y > 0 ? src.px(y0 + y - 1, x0 + x) : 0u;
+                uint32_t ul = (x > 0 && y > 0) ? src.px(y0 + y - 1, x0 + x - 1) : 0u;
+                r4 = residual4(filt[y], cur, left, up, ul);
+            }
+            const int b = (int)((r4 >> (8 * c)) & 255u);
+            atomicAdd(&s_hist[c * 256 + b], 1u);
+            if (b == prev) { ++run; }
+            else {
+                if (prev >= 0 && run >= p.L_min) { ms += (unsigned long long)run; mc += 1; }
+                prev = b; run = 1;
+            }
+        }
+        if (run >= p.L_min) { ms += (unsigned long long)run; mc += 1; }
+    }
+    if (ms) { atomicAdd(&s_ms, ms); atomicAdd(&s_mls, ms); }    // match_symbols == match_len_sum (:440-442)
+    if (mc) atomicAdd(&s_mc, mc);
+    __syncthreads();
+
+    // ---- entropy per channel with the reference's 256-leaf tree (:281-309)
+    const uint32_t n = (uint32_t)((unsigned long long)w * (unsigned long long)h);
+    for (int c = 0; c < C; ++c) {
+        double term = 0.0;
+        uint32_t hv = s_hist[c * 256 + tid];
+        if (dbg.hist) dbg.hist[c * 256 + tid] = hv;
+        if (hv) { double q = (double)hv / (double)n; term = -q * log2(q); }
+        s_red[tid] = term;
+        __syncthreads();
+        for (int st = 128; st > 0; st >>= 1) { if (tid < st) s_red[tid] += s_red[tid + st]; __syncthreads(); }
+        if (tid == 0) s_Hc[c] = s_red[0];
+        __syncthreads();
+    }
+    if (tid == 0) {
+        double H[4] = {0, 0, 0, 0};
+        for (int c = 0; c < C; ++c) H[c] = s_Hc[c];
+        const double Hbar = ((H[0] + H[2]) + (H[1] + H[3])) / (double)C;   // tree of :314-328
+        const double sz = size_formula_big(Hbar, s_ms, s_mc, s_mls, N, h, p);
+        *out = sz;
+        if (dbg.size) *dbg.size = sz;
+        if (dbg.match) { dbg.match[0] = s_ms; dbg.match[1] = s_mc; dbg.match[2] = s_mls; }
+    }
+    __syncthreads();
+}
+
+__device__ __forceinline__ bool flagged(int4 bb, int L_min) {
+    const int w = bb.z - bb.x + 1, h = bb.w - bb.y + 1;
+    if (w <= 0 || h <= 0) return false;
+    long long N = 4ll * w * h;
+    return (N + 65535) / 65536 >= (long long)L_min;
+}
+
+__global__ void __launch_bounds__(BIG_T) big_kernel(Tables t, EstParams p) {
+    const int v = blockIdx.y;
+    if (t.status[v] != ST_OK) return;
+    const int K = t.K[v];
+    const int4* bbs = t.bboxes + (int64_t)v * t.Kmax;
+    double* sizes = t.seg_sizes + (int64_t)v * t.Kmax;
+    uint8_t* filt = t.big_filter + ((int64_t)v * BIG_CTAS + blockIdx.x) * t.H;
+    BigDebug none{};
+    for (int k0 = 0; k0 < K; k0 += BIG_T) {
+        const int k = k0 + threadIdx.x;
+        const int mine = (k < K && (k % BIG_CTAS) == (int)blockIdx.x && flagged(__ldg(bbs + k), p.L_min)) ? 1 : 0;
+        if (!__syncthreads_or(mine)) continue;
+        const int kend = min(k0 + BIG_T, K);
+        for (int kk = k0 + (((int)blockIdx.x - k0) % BIG_CTAS + BIG_CTAS) % BIG_CTAS; kk < kend; kk += BIG_CTAS) {
+            const int4 bb = __ldg(bbs + kk);
+            if (!flagged(bb, p.L_min)) continue;
+            SrcPixlab src{t.pixlab + (int64_t)v * t.H * t.W, t.W, (uint32_t)kk};
+            block_segment(src, bb.x, bb.y, bb.z - bb.x + 1, bb.w - bb.y + 1, 4, p, filt, sizes + kk, none);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(BIG_T) big_debug_kernel(Tables t, EstParams p, int v, int k, BigDebug dbg) {
+    const int4 bb = t.bboxes[(int64_t)v * t.Kmax + k];
+    if (!flagged(bb, p.L_min)) return;          // the warp path's debug kernel handles it
+    __shared__ double scratch;
+    SrcPixlab src{t.pixlab + (int64_t)v * t.H * t.W, t.W, (uint32_t)k};
+    block_segment(src, bb.x, bb.y, bb.z - bb.x + 1, bb.w - bb.y + 1, 4, p, t.big_filter, &scratch, dbg);
+}
+
+__global__ void __launch_bounds__(BIG_T) single_segment_kernel(SrcRaw src, int x0, int y0, int w, int h, EstParams p,
+                                                                uint8_t* filt, double* out, BigDebug dbg) {
+    block_segment(src, x0, y0, w, h, src.C, p, filt, out, dbg);
+}
+
+cudaError_t launch_big(const Tables& t, const EstParams& p, cudaStream_t st) {
+    // no segment of an HxW map can reach chunk >= L_min unless the whole map does
+    long long chunk = (4ll * t.H * t.W + 65535) / 65536;
+    if (chunk < (long long)p.L_min) return cudaSuccess;
+    big_kernel<<<dim3(BIG_CTAS, t.V), BIG_T, 0, st>>>(t, p);
+    count_launch();
+    return cudaGetLastError();
+}
+
+cudaError_t launch_big_debug(const Tables& t, const EstParams& p, int v, int k, uint32_t* row_costs, uint8_t* filter_id,
+                             uint32_t* hist, unsigned long long* match, double* size_out, cudaStream_t st) {
+    BigDebug d{row_costs, filter_id, hist, match, size_out};
+    big_debug_kernel<<<1, BIG_T, 0, st>>>(t, p, v, k, d);
+    count_launch();
+    return cudaGetLastError();
+}
+
+cudaError_t launch_single_segment(const uint8_t* img, int W, int H, int channels, const int64_t* labels, int64_t k,
+                                  int x0, int y0, int w, int h, const EstParams& p, double* out, uint32_t* row_costs,
+                                  uint8_t* filter_id, uint32_t* hist, unsigned long long* match, uint8_t* filter_scratch,
+                                  cudaStream_t st) {
+    (void)H;
+    SrcRaw src{img, labels, W, channels, k};
+    BigDebug d{row_costs, filter_id, hist, match, nullptr};
+    single_segment_kernel<<<1, BIG_T, 0, st>>>(src, x0, y0, w, h, p, filter_scratch, out, d);
+    count_launch();
+    return cudaGetLastError();
+}
+
+}  // namespace icr

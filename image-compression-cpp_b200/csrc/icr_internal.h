@@ -48,9 +48,12 @@ cudaError_t launch_estimate(const Tables& t, const EstParams& p, cudaStream_t st
 cudaError_t launch_big(const Tables& t, const EstParams& p, cudaStream_t st);
 cudaError_t launch_reward(const Tables& t, const EstParams& p, const double* image_sizes, int S,
                           double* rewards, cudaStream_t st);
-cudaError_t launch_debug_segment(const Tables& t, int v, int k, const EstParams& p, uint32_t* row_costs,
-                                 uint8_t* filter_id, uint32_t* hist, unsigned long long* match,
-                                 double* size_out, cudaStream_t st);
+cudaError_t launch_estimate_debug(const Tables& t, const EstParams& p, int v, int k, uint32_t* row_costs,
+                                  uint8_t* filter_id, uint32_t* hist, unsigned long long* match,
+                                  double* size_out, cudaStream_t st);
+cudaError_t launch_big_debug(const Tables& t, const EstParams& p, int v, int k, uint32_t* row_costs,
+                             uint8_t* filter_id, uint32_t* hist, unsigned long long* match,
+                             double* size_out, cudaStream_t st);
 cudaError_t launch_slice(const Tables& t, int v, int k, uint8_t* out, size_t cap, cudaStream_t st);
 cudaError_t launch_compact_stats(const int64_t* labels, int H, int W, int K, int32_t* counts,
                                  int32_t* bboxes, cudaStream_t st);

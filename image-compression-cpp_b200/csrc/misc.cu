@@ -1,0 +1,193 @@
+// Small kernels around the estimator: reward epilogue (Rule W), slice materialisation (Rule P),
+// the compact-label stats drop-in (Rule S), EMA baseline + advantage (Rule E) and the self-test.
+#include "icr_internal.h"
+#include "icr_pixel.cuh"
+
+namespace icr {
+
+// ---- Rule W (src/compute_rewards.cu:183-192): one warp per label map, fixed summation order
+__global__ void __launch_bounds__(128) reward_kernel(Tables t, EstParams p, const double* __restrict__ image_sizes,
+                                                      int S, double* __restrict__ rewards) {
+    const int v = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (v >= t.V) return;
+    if (t.status[v] != ST_OK) { if (lane == 0) rewards[v] = __longlong_as_double(0x7ff8000000000000ll); return; }
+    const int K = t.K[v];
+    const double* sz = t.seg_sizes + (int64_t)v * t.Kmax;
+    const int32_t* cnt = t.counts + (int64_t)v * t.Kmax;
+    double sum = 0.0;
+    int valid = 0;
+    for (int k = lane; k < K; k += 32) { sum += sz[k]; valid += cnt[k] >= p.min_pixels ? 1 : 0; }
+    for (int o = 16; o; o >>= 1) { sum += __shfl_xor_sync(0xffffffffu, sum, o); valid += __shfl_xor_sync(0xffffffffu, valid, o); }
+    if (lane == 0) {
+        if (K <= 0) { rewards[v] = 0.0; return; }                   // :136-139
+        const double s_img = image_sizes[v / S];
+        const double P = valid == 1 ? 1.0 : 0.0;
+        rewards[v] = (s_img - sum) / s_img - p.lambda * P;
+    }
+}
+
+cudaError_t launch_reward(const Tables& t, const EstParams& p, const double* image_sizes, int S, double* rewards, cudaStream_t st) {
+    reward_kernel<<<(t.V + 3) / 4, 128, 0, st>>>(t, p, image_sizes, S, rewards);
+    count_launch();
+    return cudaGetLastError();
+}
+
+// ---- Rule P (src/image_slicer.cpp:59-66): masked bbox crop of one segment, u8 [h,w,4]
+__global__ void slice_kernel(Tables t, int v, int k, uint32_t* out, size_t cap_px) {
+    const int4 bb = t.bboxes[(int64_t)v * t.Kmax + k];
+    const int w = bb.z - bb.x + 1, h = bb.w - bb.y + 1;
+    if (w <= 0 || h <= 0) return;
+    const uint2* map = t.pixlab + (int64_t)v * t.H * t.W;
+    const int64_t n = (int64_t)w * h;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n && (size_t)i < cap_px; i += (int64_t)gridDim.x * blockDim.x) {
+        const int y = (int)(i / w), x = (int)(i - (int64_t)y * w);
+        const uint2 q = map[(int64_t)(bb.y + y) * t.W + bb.x + x];
+        out[i] = q.y == (uint32_t)k ? q.x : 0u;
+    }
+}
+
+cudaError_t launch_slice(const Tables& t, int v, int k, uint8_t* out, size_t cap, cudaStream_t st) {
+    slice_kernel<<<148, 256, 0, st>>>(t, v, k, reinterpret_cast<uint32_t*>(out), cap / 4);
+    count_launch();
+    return cudaGetLastError();
+}
+
+// ---- Rule S on already-compact int64 labels (src/segment_stats.cu:11-77)
+__global__ void compact_init_kernel(int32_t* counts, int32_t* bboxes, int K, int W, int H) {
+    int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= K) return;
+    counts[k] = 0;
+    reinterpret_cast<int4*>(bboxes)[k] = make_int4(W, H, -1, -1);
+}
+
+__global__ void __launch_bounds__(256) compact_stats_kernel(const int64_t* __restrict__ lab, int H, int W, int K,
+                                                             int32_t* counts, int32_t* bboxes) {
+    // one thread per pixel, runs of equal ids along a row collapse to one update (warp-aggregated)
+    const int64_t HW = (int64_t)H * W;
+    const int lane = threadIdx.x & 31;
+    for (int64_t base = (int64_t)blockIdx.x * blockDim.x; base < HW; base += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t p = base + threadIdx.x;
+        const bool in = p < HW;
+        const int64_t id = in ? lab[p] : -1;
+        const int y = (int)(p / W), x = (int)(p - (int64_t)y * W);
+        const int64_t pid = __shfl_up_sync(0xffffffffu, id, 1);
+        const int py = __shfl_up_sync(0xffffffffu, y, 1);
+        const bool ok = in && id >= 0 && id < K;
+        const bool joins = lane > 0 && ok && pid == id && py == y;
+        const uint32_t breaks = __ballot_sync(0xffffffffu, !joins);
+        if (ok && !joins) {
+            uint32_t above = lane == 31 ? 0u : (breaks & (0xffffffffu << (lane + 1)));
+            const int n = (above ? __ffs(above) - 1 : 32) - lane;
+            int32_t* bb = bboxes + 4 * id;
+            atomicAdd(&counts[id], n);
+            atomicMin(&bb[0], x); atomicMin(&bb[1], y); atomicMax(&bb[2], x + n - 1); atomicMax(&bb[3], y);
+        }
+    }
+}
+
+cudaError_t launch_compact_stats(const int64_t* labels, int H, int W, int K, int32_t* counts, int32_t* bboxes, cudaStream_t st) {
+    if (K > 0) { compact_init_kernel<<<(K + 255) / 256, 256, 0, st>>>(counts, bboxes, K, W, H); count_launch(); }
+    const int64_t HW = (int64_t)H * W;
+    int blocks = (int)((HW + 255) / 256);
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    if (blocks > 0) { compact_stats_kernel<<<blocks, 256, 0, st>>>(labels, H, W, K, counts, bboxes); count_launch(); }
+    return cudaGetLastError();
+}
+
+// ---- Rule E + advantage (include/ema_baseline.hpp:11-21, src/fcn/training.cpp:178-181)
+__device__ double block_sum(double v, double* sh) {
+    for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = v;
+    __syncthreads();
+    double s = 0.0;
+    for (int i = 0; i < (int)(blockDim.x >> 5); ++i) s += sh[i];
+    return s;
+}
+
+__global__ void __launch_bounds__(1024) sum_count_kernel(const double* __restrict__ r, int n, double* out) {
+    __shared__ double sh[32];
+    double s = 0.0;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) s += r[i];
+    s = block_sum(s, sh);
+    if (threadIdx.x == 0) { out[0] = s; out[1] = (double)n; }
+}
+
+__global__ void __launch_bounds__(1024) ema_kernel(const double* __restrict__ r, int n, const double* sum_count,
+                                                    double momentum, double* state, double* adv) {
+    __shared__ double sh[32];
+    double s = 0.0;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) s += r[i];
+    s = block_sum(s, sh);
+    const double local_mean = n > 0 ? s / (double)n : 0.0;
+    const double mean = sum_count ? sum_count[0] / sum_count[1] : local_mean;
+    __shared__ double s_value;
+    if (threadIdx.x == 0) {
+        double value = state[1] != 0.0 ? state[0] * momentum + mean * (1.0 - momentum) : mean;
+        state[0] = value; state[1] = 1.0;
+        s_value = value;
+    }
+    if (!adv) return;
+    // adv = (r - value); standardise: the baseline cancels in (adv - mean(adv)), std is the population std
+    double q = 0.0;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) { double d = r[i] - local_mean; q += d * d; }
+    q = block_sum(q, sh);
+    const double sd = fmax(sqrt(q / (double)n), 1e-6);
+    const double value = s_value;
+    const double adv_mean = local_mean - value;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) adv[i] = ((r[i] - value) - adv_mean) / sd;
+}
+
+cudaError_t launch_sum_count(const double* rewards, int n, double* sum_count, cudaStream_t st) {
+    sum_count_kernel<<<1, 1024, 0, st>>>(rewards, n, sum_count);
+    count_launch();
+    return cudaGetLastError();
+}
+
+cudaError_t launch_ema(const double* rewards, int n, const double* sum_count, double momentum, double* state, double* adv, cudaStream_t st) {
+    ema_kernel<<<1, 1024, 0, st>>>(rewards, n, sum_count, momentum, state, adv);
+    count_launch();
+    return cudaGetLastError();
+}
+
+// ---- exhaustive self-test of the packed-byte arithmetic against scalar code
+__global__ void selftest_kernel(unsigned int* bad) {
+    // thread = (a, b) pair; loops over c: Paeth; also Avg, absdiff/cost and vsub4 on the pair
+    const uint32_t ab = blockIdx.x * blockDim.x + threadIdx.x;     // 0..65535
+    const uint32_t a = ab & 255u, b = ab >> 8;
+    unsigned int errs = 0;
+    for (uint32_t c = 0; c < 256; c += 4) {
+        // four different c values in the four byte lanes, a and b rotated so lanes differ
+        uint32_t A = a | ((a ^ 0x55u) << 8) | (((a + 77u) & 255u) << 16) | ((255u - a) << 24);
+        uint32_t Bv = b | (((b + 131u) & 255u) << 8) | ((b ^ 0xAAu) << 16) | ((255u - b) << 24);
+        uint32_t Cv = c | ((c + 1) << 8) | ((c + 2) << 16) | ((c + 3) << 24);
+        uint32_t P = paeth4(A, Bv, Cv), G = avg4(A, Bv), D = absdiff4(A, Bv), R = __vsub4(A, Bv);
+        uint32_t cost = cost_acc(D, 7u), cost_ref = 7u;
+        for (int l = 0; l < 4; ++l) {
+            int aa = (A >> (8 * l)) & 255, bb = (Bv >> (8 * l)) & 255, cc = (Cv >> (8 * l)) & 255;
+            if ((int)((P >> (8 * l)) & 255u) != paeth1(aa, bb, cc)) ++errs;
+            if ((int)((G >> (8 * l)) & 255u) != ((aa + bb) >> 1)) ++errs;
+            if ((int)((D >> (8 * l)) & 255u) != abs(aa - bb)) ++errs;
+            if ((int)((R >> (8 * l)) & 255u) != ((aa - bb) & 255)) ++errs;
+            cost_ref += (uint32_t)abs((int)(int8_t)(uint8_t)((aa - bb) & 255));
+        }
+        if (cost != cost_ref) ++errs;
+    }
+    if (errs) atomicAdd(bad, errs);
+}
+
+cudaError_t run_selftest(int* mismatches) {
+    unsigned int* d = nullptr;
+    cudaError_t e = cudaMalloc(&d, sizeof(unsigned int));
+    if (e != cudaSuccess) return e;
+    cudaMemset(d, 0, sizeof(unsigned int));
+    selftest_kernel<<<256, 256>>>(d);
+    count_launch();
+    unsigned int h = 0;
+    e = cudaMemcpy(&h, d, sizeof h, cudaMemcpyDeviceToHost);
+    cudaFree(d);
+    *mismatches = (int)h;
+    return e;
+}
+
+}  // namespace icr
