@@ -1,0 +1,244 @@
+"""GPU parity tests proper: the CUDA path (through the C ABI) against the CPU oracle on the same seeded
+inputs.  Bit-exact for areas, bboxes, slice bytes, row costs, filter choices, histograms and match triples;
+1e-5 relative (BASELINE.json north_star) for the double-precision size estimate and reward."""
+import numpy as np
+import pytest
+import torch
+
+from image_compression_cpp_b200 import synth
+
+pytestmark = pytest.mark.gpu
+RTOL = 1e-5      # BASELINE.json: "within 1e-5 relative for the floating-point size estimate and reward"
+
+
+def _to(dev, *arrs):
+    return [torch.from_numpy(np.ascontiguousarray(a)).to(dev) for a in arrs]
+
+
+def _rel(a, b):
+    a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
+    return float(np.max(np.abs(a - b) / np.maximum(np.abs(b), 1e-300))) if a.size else 0.0
+
+
+def _run(icr, dev, images, labels, sizes, Kmax=None, **kw):
+    B, H, W = labels.shape[0], labels.shape[-2], labels.shape[-1]
+    V = int(np.prod(labels.shape[:-2]))
+    ws = icr.Workspace(dev, V, H, W, Kmax)
+    ti, tl, ts = _to(dev, images, labels, sizes)
+    r = icr.compute_rewards_batched(ti, tl, ts, workspace=ws, **kw)
+    return r.cpu().numpy(), ws
+
+
+def _check_batch(icr, orc, dev, images, labels, sizes, tables=True, n_debug=6, Kmax=None, **kw):
+    prm = orc.params(kw.get("min_pixels_per_segment", 1), kw.get("L_min", 4), kw.get("beta", 0.012167),
+                     kw.get("b_match_token", 18.0), kw.get("gamma", 0.1), kw.get("overhead_base", 9.308622),
+                     kw.get("adaptive_filter", True), kw.get("lambda_", 0.5))
+    got, ws = _run(icr, dev, images, labels, sizes, Kmax=Kmax, **kw)
+    B, _, H, W = images.shape
+    Ks = ws.Kmax
+    want, det = orc.compute_rewards(images, labels, sizes, prm, details=True, Kstride=Ks)
+    K, counts, bboxes, seg = [t.cpu().numpy() for t in ws.tables()]
+    assert np.array_equal(K[:B], det["K"])
+    for b in range(B):
+        k = det["K"][b]
+        assert np.array_equal(counts[b, :k], det["counts"][b, :k]), f"counts of image {b}"
+        assert np.array_equal(bboxes[b, :k], det["bboxes"][b, :k]), f"bboxes of image {b}"
+        assert _rel(seg[b, :k], det["seg_sizes"][b, :k]) < RTOL, f"segment sizes of image {b}"
+    assert _rel(got, want) < RTOL
+    if not tables:
+        return got, ws
+    # bytes and ids the estimator reads (Rule C, Rule L)
+    pl = ws.pixlab().cpu().numpy()
+    rng = np.random.default_rng(7)
+    for b in range(min(B, 3)):
+        rgba = orc.chw3_f32_to_rgba(images[b])
+        comp, _ = orc.compact_labels(labels[b])
+        assert np.array_equal(pl[b, :, :, 0].view(np.uint32), rgba.view(np.uint32)[:, :, 0]), "RGBA bytes"
+        assert np.array_equal(pl[b, :, :, 1], comp.astype(np.int32)), "compact ids"
+        for k in rng.choice(det["K"][b], size=min(n_debug, det["K"][b]), replace=False):
+            x0, y0, x1, y1 = det["bboxes"][b, k]
+            w, h = x1 - x0 + 1, y1 - y0 + 1
+            s, tab = orc.estimate_segment(rgba, comp, int(k), x0, y0, w, h, prm, debug=True)
+            rc, fi, hist, match, size = [t.cpu().numpy() for t in ws.debug_segment(b, int(k), h, icr.make_params(
+                prm.min_pixels, prm.L_min, prm.beta, prm.b_match_token, prm.gamma, prm.overhead_base, prm.adaptive_filter, prm.lambda_))]
+            if prm.adaptive_filter:
+                assert np.array_equal(rc.view(np.uint32), tab["row_costs"]), f"row costs b={b} k={k}"
+            assert np.array_equal(fi, tab["filter_id"]), f"filter ids b={b} k={k}"
+            assert np.array_equal(hist.view(np.uint32), tab["hist"]), f"histogram b={b} k={k}"
+            assert np.array_equal(match.view(np.uint64), tab["match"]), f"match triple b={b} k={k}"
+            assert abs(size[0] - s) <= RTOL * abs(s)
+            sl = ws.slice_segment(b, int(k), w, h).cpu().numpy()
+            assert np.array_equal(sl, orc.slice_segment(rgba, comp, int(k), x0, y0, w, h)), f"slice bytes b={b} k={k}"
+    return got, ws
+
+
+def test_selftest_packed_arithmetic(icr, dev):
+    assert icr.selftest() == 0
+
+
+def test_config2_rect_partitions(icr, orc, dev):
+    images, labels, sizes = synth.make_batch(2, B=12)
+    _check_batch(icr, orc, dev, images, labels, sizes, Kmax=512)
+
+
+def test_config1_grid_256(icr, orc, dev):
+    images, labels, sizes = synth.make_batch(1)
+    for fam in range(6):
+        images[0] = synth.image_f32_chw(fam, 256, 256, 11 + fam)
+        _check_batch(icr, orc, dev, images, labels, sizes, Kmax=64, n_debug=3)
+
+
+def test_fine_rect_partitions_many_small_segments(icr, orc, dev):
+    H = W = 96
+    images = np.stack([synth.image_f32_chw(b, H, W, 50 + b) for b in range(6)])
+    labels = np.stack([synth.rect_partition(H, W, split_prob=0.9, min_rect_count=20, seed=60 + b) * 5 - 17 for b in range(6)]).astype(np.int32)
+    _check_batch(icr, orc, dev, images, labels, np.full(6, 9000.0))
+
+
+def test_bfs_and_voronoi_partitions(icr, orc, dev):
+    H, W = 120, 136
+    images = np.stack([synth.image_f32_chw(b + 2, H, W, 70 + b) for b in range(4)])
+    labels = np.stack([synth.bfs_partition(H, W, 23, seed=1), synth.voronoi_partition(H, W, 16, 6, seed=2),
+                       synth.bfs_partition(H, W, 5, seed=3), synth.voronoi_partition(H, W, 9, 3, seed=4)]).astype(np.int32)
+    _check_batch(icr, orc, dev, images, labels, np.full(4, 20000.0))
+
+
+def test_int64_labels_and_negative_values(icr, orc, dev):
+    images, labels, sizes = synth.make_batch(2, B=3)
+    labels = labels.astype(np.int64) * 3 - 1000
+    _check_batch(icr, orc, dev, images, labels, sizes, n_debug=2)
+
+
+def test_odd_width_scalar_path(icr, orc, dev):
+    H, W = 37, 53          # W % 4 != 0: the unvectorised prep path
+    images = np.stack([synth.image_f32_chw(b, H, W, 90 + b) for b in range(3)])
+    labels = np.stack([synth.bfs_partition(H, W, 7, seed=5 + b) for b in range(3)]).astype(np.int32)
+    _check_batch(icr, orc, dev, images, labels, np.full(3, 3000.0))
+
+
+def test_quirk_unit_range_images_collapse_to_bits(icr, orc, dev):
+    rng = np.random.default_rng(3)
+    images = rng.random((2, 3, 64, 64), dtype=np.float32)          # [0,1] training-style input
+    labels = np.stack([synth.grid_partition(64, 64, 16, 16)] * 2).astype(np.int32)
+    _check_batch(icr, orc, dev, images, labels, np.full(2, 5000.0))
+
+
+def test_quirk_rounding_and_clamping(icr, orc, dev):
+    rng = np.random.default_rng(4)
+    base = rng.integers(-20, 280, (2, 3, 32, 32)).astype(np.float32)
+    images = base + np.float32(0.5)                                   # x.5 everywhere: round half to even
+    images[1] = base[1] + rng.choice(np.array([-0.5, 0.49, 0.51, 0.0], np.float32), base[1].shape)
+    labels = np.stack([synth.grid_partition(32, 32, 8, 16)] * 2).astype(np.int32)
+    _check_batch(icr, orc, dev, images, labels, np.full(2, 2000.0))
+
+
+def test_quirk_single_segment_penalty(icr, orc, dev):
+    images = np.stack([synth.image_f32_chw(2, 48, 48, 5)])
+    labels = np.full((1, 48, 48), 9, np.int32)
+    got, _ = _check_batch(icr, orc, dev, images, labels, np.array([4000.0]))
+    # exactly one valid segment: the lambda penalty applies (src/compute_rewards.cu:183-192)
+    got0, _ = _check_batch(icr, orc, dev, images, labels, np.array([4000.0]), lambda_=0.0)
+    assert abs((got0[0] - got[0]) - 0.5) < 1e-12
+
+
+def test_quirk_min_pixels_changes_only_the_penalty(icr, orc, dev):
+    H = W = 40
+    images = np.stack([synth.image_f32_chw(5, H, W, 6)])
+    labels = np.zeros((1, H, W), np.int32)
+    labels[0, 3, 4] = 1            # 1-pixel segments
+    labels[0, 20, 21] = 2
+    a, wa = _check_batch(icr, orc, dev, images, labels, np.array([3000.0]), min_pixels_per_segment=1)
+    b, wb = _check_batch(icr, orc, dev, images, labels, np.array([3000.0]), min_pixels_per_segment=8)
+    sa, sb = wa.tables()[3].cpu().numpy()[0, :3], wb.tables()[3].cpu().numpy()[0, :3]
+    assert np.array_equal(sa, sb)                  # sizes untouched (skip_check_kernel is overwritten)
+    assert abs((a[0] - b[0]) - 0.5) < 1e-12        # only the penalty term moved: 3 valid -> 1 valid
+
+
+def test_quirk_non_adaptive_is_all_paeth(icr, orc, dev):
+    images, labels, sizes = synth.make_batch(2, B=2)
+    _check_batch(icr, orc, dev, images, labels, sizes, adaptive_filter=False, n_debug=3)
+
+
+@pytest.mark.parametrize("L_min", [4, 2, 1, 7])
+def test_rule_m_whole_image_bbox_224(icr, orc, dev, L_min):
+    # one segment whose bbox is the whole 224x224 image: chunk = 4 bytes -> matches are possible at L_min<=4
+    H = W = 224
+    images = np.stack([synth.image_f32_chw(f, H, W, 8 + f) for f in (1, 2, 3)])
+    labels = np.zeros((3, H, W), np.int32)
+    labels[:, 60:90, 100:140] = 1
+    labels[2] = synth.bfs_partition(H, W, 3, seed=2)
+    _check_batch(icr, orc, dev, images, labels, np.full(3, 70000.0), L_min=L_min, n_debug=3)
+
+
+def test_rule_m_whole_image_bbox_512(icr, orc, dev):
+    H = W = 512               # chunk = 16 bytes = 4 pixels
+    images = np.stack([synth.image_f32_chw(f, H, W, 8 + f) for f in (0, 3)])
+    labels = np.zeros((2, H, W), np.int32)
+    labels[:, 200:300, 100:400] = 5
+    _check_batch(icr, orc, dev, images, labels, np.full(2, 300000.0), n_debug=2)
+
+
+def test_multi_label_maps_share_one_image(icr, orc, dev):
+    images, labels, sizes = synth.make_multi_batch(B=3, S=4, H=64, W=80)
+    ti, tl, ts = _to(dev, images, labels, sizes)
+    got = icr.compute_rewards_batched(ti, tl, ts).cpu().numpy()
+    assert got.shape == (3, 4)
+    want = orc.compute_rewards(np.repeat(images, 4, axis=0), labels.reshape(12, 64, 80), np.repeat(sizes, 4))
+    assert _rel(got.reshape(-1), want) < RTOL
+
+
+def test_many_segments_global_stats_path(icr, orc, dev):
+    # K > 2048 segments in one map: the shared-memory stats table is bypassed
+    H = W = 128
+    images = np.stack([synth.image_f32_chw(5, H, W, 3)])
+    labels = (np.arange(H * W, dtype=np.int32).reshape(1, H, W) // 3) * 2
+    _check_batch(icr, orc, dev, images, labels, np.array([30000.0]), n_debug=4)
+
+
+def test_label_spread_beyond_capacity_is_reported(icr, dev):
+    images, labels, sizes = synth.make_batch(2, B=2)
+    labels = labels.astype(np.int64)
+    labels[1, 0, 0] = 1 << 40
+    ti, tl, ts = _to(dev, images, labels, sizes)
+    with pytest.raises(RuntimeError, match="label"):
+        icr.compute_rewards_batched(ti, tl, ts)
+    r = icr.compute_rewards_batched(ti, tl, ts, check=False).cpu().numpy()
+    assert np.isfinite(r[0]) and np.isnan(r[1])
+    with pytest.raises(RuntimeError):          # the sticky flag is reported once, then cleared
+        icr.get_workspace(dev, 2, 224, 224).check()
+    icr.get_workspace(dev, 2, 224, 224).check()
+
+
+def test_reference_argument_errors(icr, dev):
+    images, labels, sizes = synth.make_batch(2, B=2)
+    ti, tl, ts = _to(dev, images, labels, sizes)
+    with pytest.raises(RuntimeError, match=r"images must be \[B,3,H,W\]"):
+        icr.compute_rewards_batched(ti[:, :2], tl, ts)
+    with pytest.raises(RuntimeError, match="float32"):
+        icr.compute_rewards_batched(ti.double(), tl, ts)
+    with pytest.raises(RuntimeError, match="labels must be CUDA"):
+        icr.compute_rewards_batched(ti, tl.cpu(), ts)
+    with pytest.raises(RuntimeError, match="image_sizes must be CUDA"):
+        icr.compute_rewards_batched(ti, tl, ts.cpu())
+    with pytest.raises(RuntimeError, match="B elements"):
+        icr.compute_rewards_batched(ti, tl, ts[:1])
+    with pytest.raises(RuntimeError, match="match images"):
+        icr.compute_rewards_batched(ti, tl[:, :100], ts)
+    # CPU images are moved to the labels' device, as the reference does (src/compute_rewards.cu:82-85)
+    r = icr.compute_rewards_batched(ti.cpu(), tl, ts)
+    assert r.is_cuda and r.dtype == torch.float64 and r.shape == (2,)
+
+
+def test_full_size_config5_shard_properties(icr, orc, dev):
+    # BASELINE config 5 shard (512 images of 224^2): size-independent properties + spot parity on a sample
+    B = 512
+    images, labels, sizes = synth.make_batch(5, B=64)
+    reps = B // 64
+    images, labels, sizes = np.tile(images, (reps, 1, 1, 1)), np.tile(labels, (reps, 1, 1)), np.tile(sizes, reps)
+    got, ws = _run(icr, dev, images, labels, sizes, Kmax=256)
+    K, counts, bboxes, seg = [t.cpu().numpy() for t in ws.tables()]
+    assert np.all(counts[np.arange(256)[None, :] < K[:, None]] > 0)
+    assert np.array_equal(np.where(np.arange(256)[None, :] < K[:, None], counts, 0).sum(1), np.full(B, 224 * 224))   # areas tile the image
+    assert np.array_equal(got[:64], got[64:128]) and np.array_equal(got[:64], got[-64:])        # deterministic across the batch
+    want = orc.compute_rewards(images[:8], labels[:8], sizes[:8])
+    assert _rel(got[:8], want) < RTOL
