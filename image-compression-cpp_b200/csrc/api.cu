@@ -15,6 +15,8 @@ struct icr_workspace {
     // device staging for the host-buffer entry
     float* st_images; void* st_labels; double* st_sizes; double* st_rewards;
     size_t st_images_bytes, st_labels_bytes;
+    int profile;           // record events between the kernels of icr_compute_rewards
+    cudaEvent_t ev[5];
 };
 
 namespace icr {
@@ -127,6 +129,7 @@ int icr_workspace_destroy(icr_workspace* ws) {
     cudaSetDevice(ws->device);
     cudaFree(ws->base);
     cudaFree(ws->st_images); cudaFree(ws->st_labels); cudaFree(ws->st_sizes); cudaFree(ws->st_rewards);
+    if (ws->ev[0]) for (int i = 0; i < 5; ++i) cudaEventDestroy(ws->ev[i]);
     delete ws;
     return ICR_OK;
 }
@@ -142,10 +145,16 @@ int icr_compute_rewards(const float* images, const void* labels, int label_dtype
     Tables t = ws->t;
     t.V = B * S;
     const EstParams p = widen(params);
+    const bool prof = ws->profile != 0;
+    if (prof) cudaEventRecord(ws->ev[0], st);
     ICR_CUDA(launch_prep(images, labels, label_dtype, B, S, t, true, st), "prep");
+    if (prof) cudaEventRecord(ws->ev[1], st);
     ICR_CUDA(launch_estimate(t, p, st), "estimate");
+    if (prof) cudaEventRecord(ws->ev[2], st);
     ICR_CUDA(launch_big(t, p, st), "big_segment");
+    if (prof) cudaEventRecord(ws->ev[3], st);
     ICR_CUDA(launch_reward(t, p, image_sizes, S, rewards, st), "reward");
+    if (prof) cudaEventRecord(ws->ev[4], st);
     return ICR_OK;
 }
 
@@ -180,6 +189,21 @@ int icr_compute_rewards_host(const float* images_h, const void* labels_h, int la
                                      ws->st_rewards, ws, stream)) return rc;
     ICR_CUDA(cudaMemcpyAsync(rewards_h, ws->st_rewards, (size_t)B * S * 8, cudaMemcpyDeviceToHost, st), "D2H rewards");
     ICR_CUDA(cudaStreamSynchronize(st), "stream sync");
+    return ICR_OK;
+}
+
+int icr_workspace_set_profile(icr_workspace* ws, int on) {
+    if (!ws) return fail(ICR_EINVAL, "workspace is null");
+    if (on && !ws->ev[0]) for (int i = 0; i < 5; ++i) ICR_CUDA(cudaEventCreate(&ws->ev[i]), "cudaEventCreate");
+    ws->profile = on ? 1 : 0;
+    return ICR_OK;
+}
+
+int icr_profile_read(icr_workspace* ws, float* ms4) {
+    if (!ws || !ms4) return fail(ICR_EINVAL, "null ptr");
+    if (!ws->ev[0]) return fail(ICR_EINVAL, "profiling was never enabled on this workspace");
+    ICR_CUDA(cudaEventSynchronize(ws->ev[4]), "cudaEventSynchronize");
+    for (int i = 0; i < 4; ++i) ICR_CUDA(cudaEventElapsedTime(&ms4[i], ws->ev[i], ws->ev[i + 1]), "cudaEventElapsedTime");
     return ICR_OK;
 }
 

@@ -29,7 +29,8 @@ SYMBOLS = ["icr_last_error", "icr_version", "icr_default_params", "icr_workspace
            "icr_workspace_destroy", "icr_compute_rewards", "icr_compute_rewards_host", "icr_check",
            "icr_label_capacity", "icr_segment_stats", "icr_counts_bboxes_from_compact_labels",
            "icr_estimate_png_size_segment", "icr_workspace_tables", "icr_debug_segment", "icr_slice_segment",
-           "icr_ema_update", "icr_reward_sum_count", "icr_selftest", "icr_launch_count"]
+           "icr_ema_update", "icr_reward_sum_count", "icr_selftest", "icr_launch_count", "icr_workspace_set_profile",
+           "icr_profile_read"]
 
 
 def lib():

@@ -141,6 +141,12 @@ int icr_reward_sum_count(const double* rewards, int n, double* sum_count, icr_st
  * (all 2^24 Paeth triples, all Avg pairs, all cost bytes): *mismatches is a host int. Synchronous. */
 int icr_selftest(int* mismatches);
 
+/* Measurement hook: with profiling on, icr_compute_rewards records CUDA events on `stream` between its
+ * kernels; icr_profile_read waits for the last call and returns the device time in ms of
+ * {prep, estimate, big_segment, reward}. */
+int icr_workspace_set_profile(icr_workspace* ws, int on);
+int icr_profile_read(icr_workspace* ws, float* ms4);
+
 /* Number of kernels this library launched on the calling thread since the last reset. */
 long long icr_launch_count(int reset);
 
