@@ -12,6 +12,7 @@ struct icr_workspace {
     char* base;            // one device allocation
     size_t bytes;
     icr::Tables t;
+    icr::Inputs in;        // the caller's buffers of the last batch call (debug/slice entries read them)
     // device staging for the host-buffer entry
     float* st_images; void* st_labels; double* st_sizes; double* st_rewards;
     size_t st_images_bytes, st_labels_bytes;
@@ -33,18 +34,20 @@ static int cuda_fail(cudaError_t e, const char* what) {
 
 static size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
 
-struct Layout { size_t pixlab, K, status, counts, bboxes, sizes, err, big_filter, clog2, total; };
+struct Layout { size_t K, status, counts, bboxes, keys, sizes, err, seg_prefix, sched, big_filter, clog2, total; };
 
 static Layout layout(int V, int H, int W, int Kmax) {
     Layout l; size_t o = 0;
-    const size_t HW = (size_t)H * W;
-    l.pixlab = o; o = align_up(o + (size_t)V * HW * sizeof(uint2));
+    (void)W;
     l.K = o; o = align_up(o + (size_t)V * 4);
     l.status = o; o = align_up(o + (size_t)V * 4);
     l.counts = o; o = align_up(o + (size_t)V * Kmax * 4);
     l.bboxes = o; o = align_up(o + (size_t)V * Kmax * 16);
+    l.keys = o; o = align_up(o + (size_t)V * Kmax * 8);
     l.sizes = o; o = align_up(o + (size_t)V * Kmax * 8);
     l.err = o; o = align_up(o + 16);
+    l.seg_prefix = o; o = align_up(o + ((size_t)V + 1) * 4);
+    l.sched = o; o = align_up(o + 16);
     l.big_filter = o; o = align_up(o + (size_t)V * BIG_CTAS * H);
     l.clog2 = o; o = align_up(o + (size_t)CLOG2_N * 8);
     l.total = o;
@@ -108,7 +111,8 @@ int icr_workspace_create(icr_workspace** out, int device, int V, int H, int W, i
     cudaError_t e = cudaMalloc((void**)&ws->base, l.total);
     if (e != cudaSuccess) { delete ws; return cuda_fail(e, "cudaMalloc(workspace)"); }
     Tables& t = ws->t;
-    t.pixlab = (uint2*)(ws->base + l.pixlab); t.K = (int32_t*)(ws->base + l.K); t.status = (int32_t*)(ws->base + l.status);
+    t.K = (int32_t*)(ws->base + l.K); t.status = (int32_t*)(ws->base + l.status);
+    t.keys = (long long*)(ws->base + l.keys); t.seg_prefix = (int32_t*)(ws->base + l.seg_prefix); t.sched = (int32_t*)(ws->base + l.sched);
     t.counts = (int32_t*)(ws->base + l.counts); t.bboxes = (int4*)(ws->base + l.bboxes); t.seg_sizes = (double*)(ws->base + l.sizes);
     t.err = (int32_t*)(ws->base + l.err); t.big_filter = (uint8_t*)(ws->base + l.big_filter); t.clog2 = (const double*)(ws->base + l.clog2);
     t.V = V; t.H = H; t.W = W; t.Kmax = Kmax;
@@ -119,6 +123,8 @@ int icr_workspace_create(icr_workspace** out, int device, int V, int H, int W, i
     if (e == cudaSuccess) e = cudaMemset(ws->base + l.K, 0, (size_t)V * 4);
     if (e == cudaSuccess) e = cudaMemset(ws->base + l.status, 0, (size_t)V * 4);
     if (e == cudaSuccess) e = cudaMemset(ws->base + l.err, 0, 16);
+    if (e == cudaSuccess) e = cudaMemset(ws->base + l.seg_prefix, 0, ((size_t)V + 1) * 4);
+    if (e == cudaSuccess) e = cudaMemset(ws->base + l.sched, 0, 16);
     if (e != cudaSuccess) { cudaFree(ws->base); delete ws; return cuda_fail(e, "workspace init"); }
     *out = ws;
     return ICR_OK;
@@ -145,13 +151,16 @@ int icr_compute_rewards(const float* images, const void* labels, int label_dtype
     Tables t = ws->t;
     t.V = B * S;
     const EstParams p = widen(params);
+    const Inputs in{images, labels, label_dtype, S};
+    ws->in = in;
+    ws->t.V = t.V;
     const bool prof = ws->profile != 0;
     if (prof) cudaEventRecord(ws->ev[0], st);
-    ICR_CUDA(launch_prep(images, labels, label_dtype, B, S, t, true, st), "prep");
+    ICR_CUDA(launch_prep(labels, label_dtype, t, nullptr, st), "prep");
     if (prof) cudaEventRecord(ws->ev[1], st);
-    ICR_CUDA(launch_estimate(t, p, st), "estimate");
+    ICR_CUDA(launch_estimate(t, in, p, st), "estimate");
     if (prof) cudaEventRecord(ws->ev[2], st);
-    ICR_CUDA(launch_big(t, p, st), "big_segment");
+    ICR_CUDA(launch_big(t, in, p, st), "big_segment");
     if (prof) cudaEventRecord(ws->ev[3], st);
     ICR_CUDA(launch_reward(t, p, image_sizes, S, rewards, st), "reward");
     if (prof) cudaEventRecord(ws->ev[4], st);
@@ -220,14 +229,16 @@ int icr_check(icr_workspace* ws, icr_stream stream, int* first_bad) {
 }
 
 int icr_segment_stats(const void* labels, int label_dtype, int V, int H, int W, int32_t* K_out, int32_t* counts,
-                      int32_t* bboxes, icr_workspace* ws, icr_stream stream) {
+                      int32_t* bboxes, int32_t* compact_out, icr_workspace* ws, icr_stream stream) {
     if (!labels) return fail(ICR_EINVAL, "null ptr");
     if (label_dtype != ICR_LABELS_I32 && label_dtype != ICR_LABELS_I64) return fail(ICR_EINVAL, "labels must be int32 or int64");
     if (int rc = check_shape(ws, V, H, W)) return rc;
     cudaStream_t st = (cudaStream_t)stream;
     Tables t = ws->t;
     t.V = V;
-    ICR_CUDA(launch_prep(nullptr, labels, label_dtype, V, 1, t, false, st), "prep");
+    ws->in = Inputs{nullptr, labels, label_dtype, 1};
+    ws->t.V = V;
+    ICR_CUDA(launch_prep(labels, label_dtype, t, compact_out, st), "prep");
     if (K_out) ICR_CUDA(cudaMemcpyAsync(K_out, t.K, (size_t)V * 4, cudaMemcpyDeviceToDevice, st), "copy K");
     if (counts) ICR_CUDA(cudaMemcpyAsync(counts, t.counts, (size_t)V * t.Kmax * 4, cudaMemcpyDeviceToDevice, st), "copy counts");
     if (bboxes) ICR_CUDA(cudaMemcpyAsync(bboxes, t.bboxes, (size_t)V * t.Kmax * 16, cudaMemcpyDeviceToDevice, st), "copy bboxes");
@@ -275,13 +286,13 @@ int icr_estimate_png_size_segment(const uint8_t* img, int full_W, int full_H, in
 }
 
 int icr_workspace_tables(icr_workspace* ws, const int32_t** K, const int32_t** counts, const int32_t** bboxes,
-                         const double** seg_sizes, const uint32_t** pixlab, int* Kmax) {
+                         const double** seg_sizes, const long long** keys, int* Kmax) {
     if (!ws) return fail(ICR_EINVAL, "workspace is null");
     if (K) *K = ws->t.K;
     if (counts) *counts = ws->t.counts;
     if (bboxes) *bboxes = (const int32_t*)ws->t.bboxes;
     if (seg_sizes) *seg_sizes = ws->t.seg_sizes;
-    if (pixlab) *pixlab = (const uint32_t*)ws->t.pixlab;
+    if (keys) *keys = ws->t.keys;
     if (Kmax) *Kmax = ws->t.Kmax;
     return ICR_OK;
 }
@@ -290,19 +301,21 @@ int icr_debug_segment(icr_workspace* ws, int v, int k, const icr_params* params,
                       uint8_t* filter_id, uint32_t* hist, unsigned long long* match, double* size_out,
                       icr_stream stream) {
     if (!ws || !params) return fail(ICR_EINVAL, "null ptr");
-    if (v < 0 || v >= ws->V || k < 0 || k >= ws->Kmax) return fail(ICR_EINVAL, "segment index out of range");
+    if (v < 0 || v >= ws->t.V || k < 0 || k >= ws->Kmax) return fail(ICR_EINVAL, "segment index out of range");
     const EstParams p = widen(params);
     cudaStream_t st = (cudaStream_t)stream;
     // both kernels test the Rule M size criterion on the device; exactly one of them acts
-    ICR_CUDA(launch_estimate_debug(ws->t, p, v, k, row_costs, filter_id, hist, match, size_out, st), "estimate debug");
-    ICR_CUDA(launch_big_debug(ws->t, p, v, k, row_costs, filter_id, hist, match, size_out, st), "big debug");
+    if (!ws->in.images) return fail(ICR_EINVAL, "no batch call has run on this workspace");
+    ICR_CUDA(launch_estimate_debug(ws->t, ws->in, p, v, k, row_costs, filter_id, hist, match, size_out, st), "estimate debug");
+    ICR_CUDA(launch_big_debug(ws->t, ws->in, p, v, k, row_costs, filter_id, hist, match, size_out, st), "big debug");
     return ICR_OK;
 }
 
 int icr_slice_segment(icr_workspace* ws, int v, int k, uint8_t* out_hw4, size_t out_capacity, icr_stream stream) {
     if (!ws || !out_hw4) return fail(ICR_EINVAL, "null ptr");
-    if (v < 0 || v >= ws->V || k < 0 || k >= ws->Kmax) return fail(ICR_EINVAL, "segment index out of range");
-    ICR_CUDA(launch_slice(ws->t, v, k, out_hw4, out_capacity, (cudaStream_t)stream), "slice");
+    if (v < 0 || v >= ws->t.V || k < 0 || k >= ws->Kmax) return fail(ICR_EINVAL, "segment index out of range");
+    if (!ws->in.images) return fail(ICR_EINVAL, "no batch call has run on this workspace");
+    ICR_CUDA(launch_slice(ws->t, ws->in, v, k, out_hw4, out_capacity, (cudaStream_t)stream), "slice");
     return ICR_OK;
 }
 

@@ -15,11 +15,15 @@ constexpr int BIG_T = 256;
 
 struct BigDebug { uint32_t* row_costs; uint8_t* filter_id; uint32_t* hist; unsigned long long* match; double* size; };
 
-struct SrcPixlab {          // the batch layout: {RGBA, compact id} per pixel
-    const uint2* base; int W; uint32_t k;
+template <typename LT>
+struct SrcPlanar {          // the batch layout: the caller's f32 planes + raw labels, masked by the segment's key
+    const float* img; const LT* lab; int64_t HW; int W; LT key;
     __device__ __forceinline__ uint32_t px(int gy, int gx) const {
-        uint2 q = __ldg(base + (int64_t)gy * W + gx);
-        return q.y == k ? q.x : 0u;
+        const int64_t i = (int64_t)gy * W + gx;
+        if (__ldg(lab + i) != key) return 0u;
+        const float r = __ldg(img + i), g = __ldg(img + HW + i), b = __ldg(img + 2 * HW + i);
+        auto tb = [](float v) { return (uint32_t)__float2int_rn(fminf(fmaxf(v, 0.f), 255.f)); };    // Rule C
+        return tb(r) | tb(g) << 8 | tb(b) << 16 | 0xff000000u;
     }
 };
 
@@ -148,17 +152,14 @@ __device__ void block_segment(const Src& src, int x0, int y0, int w, int h, int 
     __syncthreads();
 }
 
-__device__ __forceinline__ bool flagged(int4 bb, int L_min) {
-    const int w = bb.z - bb.x + 1, h = bb.w - bb.y + 1;
-    if (w <= 0 || h <= 0) return false;
-    long long N = 4ll * w * h;
-    return (N + 65535) / 65536 >= (long long)L_min;
-}
+__device__ __forceinline__ bool flagged(int4 bb, int L_min) { return for_big_kernel(bb.z - bb.x + 1, bb.w - bb.y + 1, L_min); }
 
-__global__ void __launch_bounds__(BIG_T) big_kernel(Tables t, EstParams p) {
+template <typename LT>
+__global__ void __launch_bounds__(BIG_T) big_kernel(Tables t, Inputs in, EstParams p) {
     const int v = blockIdx.y;
     if (t.status[v] != ST_OK) return;
     const int K = t.K[v];
+    const int64_t HW = (int64_t)t.H * t.W;
     const int4* bbs = t.bboxes + (int64_t)v * t.Kmax;
     double* sizes = t.seg_sizes + (int64_t)v * t.Kmax;
     uint8_t* filt = t.big_filter + ((int64_t)v * BIG_CTAS + blockIdx.x) * t.H;
@@ -171,17 +172,21 @@ __global__ void __launch_bounds__(BIG_T) big_kernel(Tables t, EstParams p) {
         for (int kk = k0 + (((int)blockIdx.x - k0) % BIG_CTAS + BIG_CTAS) % BIG_CTAS; kk < kend; kk += BIG_CTAS) {
             const int4 bb = __ldg(bbs + kk);
             if (!flagged(bb, p.L_min)) continue;
-            SrcPixlab src{t.pixlab + (int64_t)v * t.H * t.W, t.W, (uint32_t)kk};
+            SrcPlanar<LT> src{in.images + (int64_t)(v / in.S) * 3 * HW, static_cast<const LT*>(in.labels) + (int64_t)v * HW, HW, t.W,
+                              (LT)t.keys[(int64_t)v * t.Kmax + kk]};
             block_segment(src, bb.x, bb.y, bb.z - bb.x + 1, bb.w - bb.y + 1, 4, p, filt, sizes + kk, none);
         }
     }
 }
 
-__global__ void __launch_bounds__(BIG_T) big_debug_kernel(Tables t, EstParams p, int v, int k, BigDebug dbg) {
+template <typename LT>
+__global__ void __launch_bounds__(BIG_T) big_debug_kernel(Tables t, Inputs in, EstParams p, int v, int k, BigDebug dbg) {
     const int4 bb = t.bboxes[(int64_t)v * t.Kmax + k];
     if (!flagged(bb, p.L_min)) return;          // the warp path's debug kernel handles it
     __shared__ double scratch;
-    SrcPixlab src{t.pixlab + (int64_t)v * t.H * t.W, t.W, (uint32_t)k};
+    const int64_t HW = (int64_t)t.H * t.W;
+    SrcPlanar<LT> src{in.images + (int64_t)(v / in.S) * 3 * HW, static_cast<const LT*>(in.labels) + (int64_t)v * HW, HW, t.W,
+                      (LT)t.keys[(int64_t)v * t.Kmax + k]};
     block_segment(src, bb.x, bb.y, bb.z - bb.x + 1, bb.w - bb.y + 1, 4, p, t.big_filter, &scratch, dbg);
 }
 
@@ -190,19 +195,20 @@ __global__ void __launch_bounds__(BIG_T) single_segment_kernel(SrcRaw src, int x
     block_segment(src, x0, y0, w, h, src.C, p, filt, out, dbg);
 }
 
-cudaError_t launch_big(const Tables& t, const EstParams& p, cudaStream_t st) {
-    // no segment of an HxW map can reach chunk >= L_min unless the whole map does
-    long long chunk = (4ll * t.H * t.W + 65535) / 65536;
-    if (chunk < (long long)p.L_min) return cudaSuccess;
-    big_kernel<<<dim3(BIG_CTAS, t.V), BIG_T, 0, st>>>(t, p);
+cudaError_t launch_big(const Tables& t, const Inputs& in, const EstParams& p, cudaStream_t st) {
+    // no segment of an HxW map can need this kernel unless the whole map would
+    if (!for_big_kernel(t.W, t.H, p.L_min)) return cudaSuccess;
+    if (in.label_dtype == ICR_LABELS_I64) big_kernel<int64_t><<<dim3(BIG_CTAS, t.V), BIG_T, 0, st>>>(t, in, p);
+    else big_kernel<int32_t><<<dim3(BIG_CTAS, t.V), BIG_T, 0, st>>>(t, in, p);
     count_launch();
     return cudaGetLastError();
 }
 
-cudaError_t launch_big_debug(const Tables& t, const EstParams& p, int v, int k, uint32_t* row_costs, uint8_t* filter_id,
-                             uint32_t* hist, unsigned long long* match, double* size_out, cudaStream_t st) {
+cudaError_t launch_big_debug(const Tables& t, const Inputs& in, const EstParams& p, int v, int k, uint32_t* row_costs,
+                             uint8_t* filter_id, uint32_t* hist, unsigned long long* match, double* size_out, cudaStream_t st) {
     BigDebug d{row_costs, filter_id, hist, match, size_out};
-    big_debug_kernel<<<1, BIG_T, 0, st>>>(t, p, v, k, d);
+    if (in.label_dtype == ICR_LABELS_I64) big_debug_kernel<int64_t><<<1, BIG_T, 0, st>>>(t, in, p, v, k, d);
+    else big_debug_kernel<int32_t><<<1, BIG_T, 0, st>>>(t, in, p, v, k, d);
     count_launch();
     return cudaGetLastError();
 }

@@ -1,23 +1,27 @@
-// estimate: Rules P, F, R, H, Z for every (label map, segment) of the batch in ONE launch.
-// Replaces the reference's 13 stream operations per segment (src/png_size_estimator.cu:505-590)
-// and its two nested host loops (src/compute_rewards.cu:125,159).
+// estimate: Rules C, P, F, R, H, Z for every (label map, segment) of the batch in ONE launch.
+// Replaces the reference's 13 stream operations per segment (src/png_size_estimator.cu:505-590),
+// its two nested host loops (src/compute_rewards.cu:125,159) and its RGBA staging kernel (:23-53).
 //
-// One warp owns one segment.  A lane owns a (row, column-strip) of the segment's bbox and walks
-// it left to right: `left` and `up-left` live in registers, `up` comes from the lane that owns
-// the row above (one shuffle), so each bbox pixel costs one 64-bit load {RGBA, id}, one compare
-// for the mask (Rule P) and the packed-byte filter arithmetic of icr_pixel.cuh.  Row costs are
-// lane-local (plus a log2(strips)-step butterfly), the filter is chosen in registers, and the
-// row is walked a second time for the residual histogram, which lives in a per-warp 4x256 table
-// in shared memory.  Zero residuals (the bulk: every masked-out pixel away from the segment) are
-// never sent to the table; bin 0 is recovered as w*h minus the rest.  No residual stream is
-// ever written.  Segments large enough for Rule M match statistics (chunk >= L_min) are left to
-// the big-segment kernel.
+// Persistent warps pull segments from the flat work list prep built (4 at a time, one global atomic).
+// A warp owns one segment.  It walks the bbox in groups of R rows: lanes along x stage the group
+// into a shared-memory tile with coalesced loads straight from the caller's buffers -- raw label
+// compared with the segment's key (Rule P), three f32 planes clamped/rounded/packed to RGBA
+// (Rule C) -- so a masked pixel is one 32-bit word.  Then every lane owns a (row, strip<=8 px) of
+// the tile: neighbours come from the tile (the row above the group stays in a rolling slot, a zero
+// guard column stands left of x=0), the five filter costs are accumulated with packed-byte
+// arithmetic in registers, strips of a row are combined by a butterfly, the filter is chosen, and
+// the chosen filter's residual bytes go to a per-warp 4x256 histogram in shared memory.  Zero
+// residuals are never sent to the table; bin 0 is recovered as w*h minus the rest.  No residual
+// stream, RGBA plane or compact-id plane is ever written to memory.  Segments that need Rule M
+// match statistics (chunk >= L_min) or are wider than 256 px are left to the big-segment kernel.
 #include "icr_internal.h"
 #include "icr_pixel.cuh"
 
 namespace icr {
 
-constexpr int EST_WARPS = 8;
+constexpr int EST_WARPS = 4;
+constexpr int TILE_WORDS = 544;       // max over strip counts of (R+1)*(S*sw+2) + read-ahead padding
+constexpr int GRAB = 4;               // segments taken per global atomic
 
 struct DebugOut {
     int v, k;
@@ -39,60 +43,94 @@ __device__ __forceinline__ double size_formula(double Hbar, unsigned long long m
     return (p.overhead + (double)h) + ((double)N * b_data) / 8.0;
 }
 
-__device__ __forceinline__ bool needs_match_stats(int w, int h, int L_min) {
-    // Rule M: chunk = ceil(N/65536); a run never leaves its chunk, so nothing matches when chunk < L_min
-    long long N = 4ll * w * h;
-    long long chunk = (N + 65535) / 65536;
-    return chunk >= (long long)L_min;
+__device__ __forceinline__ uint32_t to_byte(float v) {   // Rule C (src/compute_rewards.cu:15-20)
+    return (uint32_t)__float2int_rn(fminf(fmaxf(v, 0.f), 255.f));
 }
 
-__device__ __forceinline__ uint32_t masked(uint2 q, uint32_t k) { return q.y == k ? q.x : 0u; }
+template <typename LT>
+__device__ __forceinline__ uint32_t masked_rgba(const float* __restrict__ img, const LT* __restrict__ lab,
+                                                int64_t HW, int64_t idx, LT key) {
+    if (__ldg(lab + idx) != key) return 0u;
+    const float r = __ldg(img + idx), g = __ldg(img + HW + idx), b = __ldg(img + 2 * HW + idx);
+    return to_byte(r) | to_byte(g) << 8 | to_byte(b) << 16 | 0xff000000u;
+}
 
-template <bool DEBUG>
-__device__ void warp_segment(const uint2* __restrict__ map, int W, uint32_t k, int4 bb, uint32_t* hist,
-                             const EstParams& p, const double* __restrict__ clog2, double* out, const DebugOut& dbg) {
+template <typename LT, bool DEBUG>
+__device__ void warp_segment(const float* __restrict__ img, const LT* __restrict__ lab, int64_t HW, int W, LT key,
+                             int4 bb, uint32_t* hist, uint32_t* tile, const EstParams& p,
+                             const double* __restrict__ clog2, double* out, const DebugOut& dbg) {
     const int lane = threadIdx.x & 31;
     const int w = bb.z - bb.x + 1, h = bb.w - bb.y + 1;
     if (w <= 0 || h <= 0) { if (lane == 0) *out = 0.0; return; }   // src/compute_rewards.cu:164
 
-    // strips per row: the power of two that minimises (row groups) x (strip width)
+    // strips per row S = 2^lg with strip width sw <= 8; among those minimise (row groups) x (strip width + fixed cost)
     int lg = 0;
     {
         int best = 0x7fffffff;
         for (int l = 0; l <= 5; ++l) {
-            int S = 1 << l;
-            int cost = ((h * S + 31) >> 5) * ((w + S - 1) >> l);
+            const int swl = (w + (1 << l) - 1) >> l;
+            if (swl > 8) continue;
+            const int cost = (((h << l) + 31) >> 5) * (swl + 3);
             if (cost < best) { best = cost; lg = l; }
         }
     }
     const int S = 1 << lg, R = 32 >> lg;
     const int sr = lane >> lg, stp = lane & (S - 1);
     const int sw = (w + S - 1) >> lg;
-    const int xs = stp * sw, xe = min(xs + sw, w);
+    const int xs = stp * sw;
+    const int nstrip = max(0, min(sw, w - xs));
+    const int stride = (S * sw + 1) | 1;                 // guard column + row, odd so rows land on different banks
+    // staging geometry: lanes along x, tw = power of two covering min(w, 32)
+    int twl = 0;
+    while ((1 << twl) < w && twl < 5) ++twl;
+    const int tx = lane & ((1 << twl) - 1), ty = lane >> twl, rpp = 32 >> twl;
+
+    // zero the guard column of every slot and the slot of row -1
+    for (int s = lane; s <= R; s += 32) tile[s * stride] = 0u;
+    for (int x = lane; x < stride + 8; x += 32) tile[x] = 0u;
+    int s0 = 1;                                          // slot of the group's first row; row y lives in slot (y+1) mod (R+1)
+    const float* imgp = img + (int64_t)bb.y * W + bb.x;
+    const LT* labp = lab + (int64_t)bb.y * W + bb.x;
 
     for (int yb = 0; yb < h; yb += R) {
-        const int y = yb + sr;
-        const bool rowact = y < h;
-        const uint2* rowp = map + (int64_t)(bb.y + y) * W + bb.x;
-        const uint2* upp = rowp - W;
-        const bool has_up = y > 0;
-        uint32_t left0 = 0, upleft0 = 0;
-        if (rowact && xs > 0 && xs < xe) {
-            left0 = masked(__ldg(rowp + xs - 1), k);
-            if (has_up) upleft0 = masked(__ldg(upp + xs - 1), k);
+        __syncwarp();
+        // ---- stage rows yb .. yb+R-1 (coalesced along x), masked and packed
+        for (int r0 = 0; r0 < R; r0 += rpp) {
+            const int rr = r0 + ty, yy = yb + rr;
+            if (rr < R && yy < h) {
+                int slot = s0 + rr; if (slot > R) slot -= R + 1;
+                uint32_t* trow = tile + slot * stride + 1;
+                const int64_t rowoff = (int64_t)yy * W;
+                for (int x = tx; x < w; x += (1 << twl)) trow[x] = masked_rgba<LT>(imgp, labp, HW, rowoff + x, key);
+            }
         }
+        __syncwarp();
+        // ---- lane = (row sr of the group, strip stp)
+        const int y = yb + sr;
+        const int n = y < h ? nstrip : 0;
+        int slot = s0 + sr; if (slot > R) slot -= R + 1;
+        const int uslot = slot == 0 ? R : slot - 1;
+        const uint32_t* base = tile + slot * stride + 1 + xs;
+        const uint32_t* ub = tile + uslot * stride + 1 + xs;
+        uint32_t cur[8], up[8], pa[8], pp[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { cur[i] = base[i]; up[i] = ub[i]; }
+        const uint32_t left0 = base[-1], ul0 = ub[-1];
         int f = 4;
         if (p.adaptive) {
             Costs5 c = {0, 0, 0, 0, 0};
-            uint32_t left = left0, upleft = upleft0;
-            for (int i = 0; i < sw; ++i) {
-                const int x = xs + i;
-                const bool valid = rowact && x < xe;
-                uint32_t cur = valid ? masked(__ldg(rowp + x), k) : 0u;
-                uint32_t up = __shfl_up_sync(0xffffffffu, cur, S);
-                if (sr == 0) up = (valid && has_up) ? masked(__ldg(upp + x), k) : 0u;
-                if (valid) add_costs(c, cur, left, up, upleft);
-                left = cur; upleft = up;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const uint32_t left = i ? cur[i - 1] : left0, ul = i ? up[i - 1] : ul0;
+                pa[i] = avg4(left, up[i]);
+                pp[i] = paeth4(left, up[i], ul);
+                if (i < n) {
+                    c.none = cost_acc(cur[i], c.none);
+                    c.sub = cost_acc(absdiff4(cur[i], left), c.sub);
+                    c.up = cost_acc(absdiff4(cur[i], up[i]), c.up);
+                    c.avg = cost_acc(absdiff4(cur[i], pa[i]), c.avg);
+                    c.paeth = cost_acc(absdiff4(cur[i], pp[i]), c.paeth);
+                }
             }
             for (int o = 1; o < S; o <<= 1) {
                 c.none += __shfl_xor_sync(0xffffffffu, c.none, o);
@@ -102,38 +140,41 @@ __device__ void warp_segment(const uint2* __restrict__ map, int W, uint32_t k, i
                 c.paeth += __shfl_xor_sync(0xffffffffu, c.paeth, o);
             }
             f = pick_filter(c);
-            if (DEBUG && rowact && stp == 0 && dbg.row_costs) {
+            if (DEBUG && y < h && stp == 0 && dbg.row_costs) {
                 uint32_t* rc = dbg.row_costs + 5 * y;
                 rc[0] = c.none; rc[1] = c.sub; rc[2] = c.up; rc[3] = c.avg; rc[4] = c.paeth;
             }
+        } else {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) { pa[i] = 0u; pp[i] = paeth4(i ? cur[i - 1] : left0, up[i], i ? up[i - 1] : ul0); }
         }
-        if (DEBUG && rowact && stp == 0 && dbg.filter_id) dbg.filter_id[y] = (uint8_t)f;
-        {
-            uint32_t left = left0, upleft = upleft0;
-            for (int i = 0; i < sw; ++i) {
-                const int x = xs + i;
-                const bool valid = rowact && x < xe;
-                uint32_t cur = valid ? masked(__ldg(rowp + x), k) : 0u;
-                uint32_t up = __shfl_up_sync(0xffffffffu, cur, S);
-                if (sr == 0) up = (valid && has_up) ? masked(__ldg(upp + x), k) : 0u;
-                if (valid) {
-                    uint32_t r = residual4(f, cur, left, up, upleft);
-                    if (r) {
-                        uint32_t b0 = r & 255u, b1 = (r >> 8) & 255u, b2 = (r >> 16) & 255u, b3 = r >> 24;
-                        if (b0) atomicAdd(&hist[b0], 1u);
-                        if (b1) atomicAdd(&hist[256 + b1], 1u);
-                        if (b2) atomicAdd(&hist[512 + b2], 1u);
-                        if (b3) atomicAdd(&hist[768 + b3], 1u);
-                    }
+        if (DEBUG && y < h && stp == 0 && dbg.filter_id) dbg.filter_id[y] = (uint8_t)f;
+        // ---- residual bytes of the chosen filter -> histogram (Rules R, H)
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            if (i < n) {
+                const uint32_t left = i ? cur[i - 1] : left0;
+                uint32_t pred = f == 1 ? left : 0u;
+                if (f == 2) pred = up[i];
+                if (f == 3) pred = pa[i];
+                if (f == 4) pred = pp[i];
+                const uint32_t r = __vsub4(cur[i], pred);
+                if (r) {
+                    const uint32_t a0 = (r << 2) & 0x3fcu, a1 = (r >> 6) & 0x3fcu, a2 = (r >> 14) & 0x3fcu, a3 = (r >> 22) & 0x3fcu;
+                    char* hb = reinterpret_cast<char*>(hist);
+                    if (a0) atomicAdd(reinterpret_cast<uint32_t*>(hb + a0), 1u);
+                    if (a1) atomicAdd(reinterpret_cast<uint32_t*>(hb + 1024 + a1), 1u);
+                    if (a2) atomicAdd(reinterpret_cast<uint32_t*>(hb + 2048 + a2), 1u);
+                    if (a3) atomicAdd(reinterpret_cast<uint32_t*>(hb + 3072 + a3), 1u);
                 }
-                left = cur; upleft = up;
             }
         }
+        s0 = s0 == 0 ? R : s0 - 1;                       // (yb + R + 1) mod (R+1)
     }
     __syncwarp();
 
     // Rule H: H_c = -sum p log2 p = log2(n) - (sum c log2 c)/n ; lane owns 32 bins of channel lane/8
-    const uint32_t n = (uint32_t)w * (uint32_t)h;
+    const uint32_t npx = (uint32_t)w * (uint32_t)h;
     double acc = 0.0;
     uint32_t nz = 0;
     uint4* h4 = reinterpret_cast<uint4*>(hist) + lane * 8;
@@ -156,15 +197,15 @@ __device__ void warp_segment(const uint2* __restrict__ map, int W, uint32_t k, i
         acc += __shfl_xor_sync(0xffffffffu, acc, o);
         nz += __shfl_xor_sync(0xffffffffu, nz, o);
     }
-    const uint32_t zeros = n - nz;
+    const uint32_t zeros = npx - nz;
     if (zeros) acc += clog2_of(zeros, clog2);
     if (DEBUG && dbg.hist) { __syncwarp(); if ((lane & 7) == 0) dbg.hist[(lane >> 3) * 256] = zeros; }
-    const double Hc = log2((double)n) - acc / (double)n;
+    const double Hc = log2((double)npx) - acc / (double)npx;
     const double H0 = __shfl_sync(0xffffffffu, Hc, 0), H1 = __shfl_sync(0xffffffffu, Hc, 8);
     const double H2 = __shfl_sync(0xffffffffu, Hc, 16), H3 = __shfl_sync(0xffffffffu, Hc, 24);
     if (lane == 0) {
         const double Hbar = ((H0 + H2) + (H1 + H3)) / 4.0;     // tree of mean_channels_kernel (:314-328)
-        const double sz = size_formula(Hbar, 0, 0, 0, 4ull * n, h, p);
+        const double sz = size_formula(Hbar, 0, 0, 0, 4ull * npx, h, p);
         *out = sz;
         if (DEBUG) {
             if (dbg.match) { dbg.match[0] = 0; dbg.match[1] = 0; dbg.match[2] = 0; }
@@ -173,53 +214,86 @@ __device__ void warp_segment(const uint2* __restrict__ map, int W, uint32_t k, i
     }
 }
 
-__global__ void __launch_bounds__(EST_WARPS * 32) estimate_kernel(Tables t, EstParams p) {
+template <typename LT>
+__global__ void __launch_bounds__(EST_WARPS * 32) estimate_kernel(Tables t, Inputs in, EstParams p) {
     __shared__ __align__(16) uint32_t hist_all[EST_WARPS][1024];
-    const int v = blockIdx.y;
-    const int warp = threadIdx.x >> 5;
+    __shared__ uint32_t tile_all[EST_WARPS][TILE_WORDS];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     uint32_t* hist = hist_all[warp];
-    for (int i = threadIdx.x & 31; i < 1024; i += 32) hist[i] = 0;
+    for (int i = lane; i < 1024; i += 32) hist[i] = 0;
     __syncwarp();
-    if (t.status[v] != ST_OK) return;
-    const int K = t.K[v];
-    const uint2* map = t.pixlab + (int64_t)v * t.H * t.W;
-    const int4* bbs = t.bboxes + (int64_t)v * t.Kmax;
-    double* sizes = t.seg_sizes + (int64_t)v * t.Kmax;
+    const int64_t HW = (int64_t)t.H * t.W;
+    const int total = t.seg_prefix[t.V];
+    const LT* labels = static_cast<const LT*>(in.labels);
     DebugOut none{};
-    for (int k = blockIdx.x * EST_WARPS + warp; k < K; k += gridDim.x * EST_WARPS) {
-        const int4 bb = __ldg(bbs + k);
-        if (needs_match_stats(bb.z - bb.x + 1, bb.w - bb.y + 1, p.L_min)) continue;   // big-segment kernel
-        warp_segment<false>(map, t.W, (uint32_t)k, bb, hist, p, t.clog2, sizes + k, none);
+    for (;;) {
+        int base = lane == 0 ? atomicAdd(&t.sched[1], GRAB) : 0;
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (base >= total) break;
+        // lanes 0..GRAB-1 locate their flat index: the map v with seg_prefix[v] <= flat < seg_prefix[v+1]
+        int mv = 0, mk = 0;
+        if (lane < GRAB && base + lane < total) {
+            const int flat = base + lane;
+            int lo = 0, hi = t.V;                       // invariant: seg_prefix[lo] <= flat < seg_prefix[hi]
+            while (hi - lo > 1) { int mid = (lo + hi) >> 1; if (__ldg(t.seg_prefix + mid) <= flat) lo = mid; else hi = mid; }
+            mv = lo; mk = flat - __ldg(t.seg_prefix + lo);
+        }
+        const int cnt = min(GRAB, total - base);
+        for (int j = 0; j < cnt; ++j) {
+            const int v = __shfl_sync(0xffffffffu, mv, j), k = __shfl_sync(0xffffffffu, mk, j);
+            const int4 bb = __ldg(t.bboxes + (int64_t)v * t.Kmax + k);
+            if (for_big_kernel(bb.z - bb.x + 1, bb.w - bb.y + 1, p.L_min)) continue;
+            const LT key = (LT)__ldg(t.keys + (int64_t)v * t.Kmax + k);
+            warp_segment<LT, false>(in.images + (int64_t)(v / in.S) * 3 * HW, labels + (int64_t)v * HW, HW, t.W, key, bb,
+                                    hist, tile_all[warp], p, t.clog2, t.seg_sizes + (int64_t)v * t.Kmax + k, none);
+        }
     }
 }
 
-__global__ void __launch_bounds__(32) estimate_debug_kernel(Tables t, EstParams p, DebugOut dbg) {
+template <typename LT>
+__global__ void __launch_bounds__(32) estimate_debug_kernel(Tables t, Inputs in, EstParams p, DebugOut dbg) {
     __shared__ __align__(16) uint32_t hist[1024];
+    __shared__ uint32_t tile[TILE_WORDS];
     for (int i = threadIdx.x; i < 1024; i += 32) hist[i] = 0;
     __syncwarp();
-    const uint2* map = t.pixlab + (int64_t)dbg.v * t.H * t.W;
+    const int64_t HW = (int64_t)t.H * t.W;
     const int4 bb = t.bboxes[(int64_t)dbg.v * t.Kmax + dbg.k];
+    if (for_big_kernel(bb.z - bb.x + 1, bb.w - bb.y + 1, p.L_min)) return;     // the big-segment debug kernel acts
+    const LT key = (LT)t.keys[(int64_t)dbg.v * t.Kmax + dbg.k];
     double scratch;
-    warp_segment<true>(map, t.W, (uint32_t)dbg.k, bb, hist, p, t.clog2, dbg.size ? dbg.size : &scratch, dbg);
+    warp_segment<LT, true>(in.images + (int64_t)(dbg.v / in.S) * 3 * HW, static_cast<const LT*>(in.labels) + (int64_t)dbg.v * HW,
+                           HW, t.W, key, bb, hist, tile, p, t.clog2, dbg.size ? dbg.size : &scratch, dbg);
 }
 
-cudaError_t launch_estimate(const Tables& t, const EstParams& p, cudaStream_t st) {
-    // enough CTAs to fill 148 SMs several times over, never more than the segments can use
-    int gx = (2368 + t.V - 1) / t.V;
-    int need = (t.Kmax + EST_WARPS - 1) / EST_WARPS;
-    if (gx > need) gx = need;
-    if (gx < 1) gx = 1;
-    dim3 grid(gx, t.V);
-    estimate_kernel<<<grid, EST_WARPS * 32, 0, st>>>(t, p);
+static int est_grid() {
+    static int g = 0;
+    if (!g) {
+        int dev = 0, sms = 148, a = 0, b = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&a, estimate_kernel<int32_t>, EST_WARPS * 32, 0);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, estimate_kernel<int64_t>, EST_WARPS * 32, 0);
+        int per = a < b ? a : b;
+        if (per < 1) per = 1;
+        g = sms * per;
+    }
+    return g;
+}
+
+cudaError_t launch_estimate(const Tables& t, const Inputs& in, const EstParams& p, cudaStream_t st) {
+    const int grid = est_grid();     // persistent: every CTA resident, warps pull work until the list is empty
+    if (in.label_dtype == ICR_LABELS_I64) estimate_kernel<int64_t><<<grid, EST_WARPS * 32, 0, st>>>(t, in, p);
+    else estimate_kernel<int32_t><<<grid, EST_WARPS * 32, 0, st>>>(t, in, p);
     count_launch();
     return cudaGetLastError();
 }
 
-cudaError_t launch_estimate_debug(const Tables& t, const EstParams& p, int v, int k, uint32_t* row_costs,
+cudaError_t launch_estimate_debug(const Tables& t, const Inputs& in, const EstParams& p, int v, int k, uint32_t* row_costs,
                                   uint8_t* filter_id, uint32_t* hist, unsigned long long* match, double* size_out,
                                   cudaStream_t st) {
     DebugOut d{v, k, row_costs, filter_id, hist, match, size_out};
-    estimate_debug_kernel<<<1, 32, 0, st>>>(t, p, d);
+    if (in.label_dtype == ICR_LABELS_I64) estimate_debug_kernel<int64_t><<<1, 32, 0, st>>>(t, in, p, d);
+    else estimate_debug_kernel<int32_t><<<1, 32, 0, st>>>(t, in, p, d);
     count_launch();
     return cudaGetLastError();
 }

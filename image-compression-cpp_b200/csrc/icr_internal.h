@@ -13,48 +13,66 @@ constexpr int KS_SMEM = 2048;          // per-CTA shared-memory stats table entr
 constexpr int64_t LCAP_MAX = 1 << 19;  // label bitmap capacity (bits) that fits shared memory
 
 struct Tables {            // device pointers into the workspace, V label maps
-    uint2* pixlab;         // [V,H,W] {RGBA bytes, compact id}
     int32_t* K;            // [V]
     int32_t* status;       // [V]
     int32_t* counts;       // [V,Kmax]
     int4* bboxes;          // [V,Kmax] (x0,y0,x1,y1) inclusive
+    long long* keys;       // [V,Kmax] original label value of compact id k (ascending: Rule L)
     double* seg_sizes;     // [V,Kmax]
-    int32_t* err;          // [2] {any-error flag, first bad map + 1}
+    int32_t* err;          // [2] {any-error flag, 0x7fffffff - first bad map}
+    int32_t* seg_prefix;   // [V+1] exclusive scan of the segment counts of the maps with status OK
+    int32_t* sched;        // [4] {prep CTAs done, estimate work cursor, -, -}
     uint8_t* big_filter;   // [V*BIG_CTAS, H] filter ids of the segment a big-kernel CTA is working on
     const double* clog2;   // [CLOG2_N] c*log2(c)
     int V, H, W, Kmax;
 };
 
+struct Inputs {            // the caller's device buffers of the current call
+    const float* images;   // [B,3,H,W] planar f32
+    const void* labels;    // [B*S,H,W]
+    int label_dtype;       // ICR_LABELS_I32 / ICR_LABELS_I64
+    int S;                 // label maps per image
+};
+
 constexpr int BIG_CTAS = 2;       // big-segment CTAs per label map
 constexpr int CLOG2_N = 4096;
+constexpr int EST_MAX_W = 256;    // widest bbox the warp path holds in registers (32 strips of 8 pixels)
+constexpr int EST_MAX_AREA = 1 << 20;
+
+// Segments the warp path leaves to the big-segment kernel: Rule M can fire (chunk = ceil(N/65536) >= L_min,
+// src/png_size_estimator.cu:416-451), or the bbox is wider than 32 register strips, or very large.
+__host__ __device__ inline bool for_big_kernel(int w, int h, int L_min) {
+    if (w <= 0 || h <= 0) return false;
+    long long N = 4ll * w * h;
+    return (N + 65535) / 65536 >= (long long)L_min || w > EST_MAX_W || (long long)w * h > EST_MAX_AREA;
+}
 
 struct EstParams {         // icr_params widened the way the reference does (:588)
     int32_t min_pixels, L_min, adaptive;
     double beta, token, gamma, overhead, lambda;
 };
 
-// label capacity (bits of the presence bitmap) for an HxW map
+// label capacity (bits of the circular presence bitmap) for an HxW map: a power of two >= max(H*W, 65536)
 inline int64_t label_capacity(int H, int W) {
     int64_t hw = (int64_t)H * W;
-    int64_t cap = hw < 65536 ? 65536 : hw;
-    cap = (cap + 1023) / 1024 * 1024;
+    int64_t cap = 65536;
+    while (cap < hw) cap <<= 1;
     return cap;
 }
 
 // launchers (each returns the cudaError_t of its launches)
-cudaError_t launch_prep(const float* images, const void* labels, int label_dtype, int B, int S,
-                        const Tables& t, bool convert_pixels, cudaStream_t st);
-cudaError_t launch_estimate(const Tables& t, const EstParams& p, cudaStream_t st);
-cudaError_t launch_big(const Tables& t, const EstParams& p, cudaStream_t st);
+cudaError_t launch_prep(const void* labels, int label_dtype, const Tables& t, int32_t* compact_out, cudaStream_t st);
+cudaError_t launch_estimate(const Tables& t, const Inputs& in, const EstParams& p, cudaStream_t st);
+cudaError_t launch_big(const Tables& t, const Inputs& in, const EstParams& p, cudaStream_t st);
 cudaError_t launch_reward(const Tables& t, const EstParams& p, const double* image_sizes, int S,
                           double* rewards, cudaStream_t st);
-cudaError_t launch_estimate_debug(const Tables& t, const EstParams& p, int v, int k, uint32_t* row_costs,
+cudaError_t launch_estimate_debug(const Tables& t, const Inputs& in, const EstParams& p, int v, int k, uint32_t* row_costs,
                                   uint8_t* filter_id, uint32_t* hist, unsigned long long* match,
                                   double* size_out, cudaStream_t st);
-cudaError_t launch_big_debug(const Tables& t, const EstParams& p, int v, int k, uint32_t* row_costs,
+cudaError_t launch_big_debug(const Tables& t, const Inputs& in, const EstParams& p, int v, int k, uint32_t* row_costs,
                              uint8_t* filter_id, uint32_t* hist, unsigned long long* match,
                              double* size_out, cudaStream_t st);
-cudaError_t launch_slice(const Tables& t, int v, int k, uint8_t* out, size_t cap, cudaStream_t st);
+cudaError_t launch_slice(const Tables& t, const Inputs& in, int v, int k, uint8_t* out, size_t cap, cudaStream_t st);
 cudaError_t launch_compact_stats(const int64_t* labels, int H, int W, int K, int32_t* counts,
                                  int32_t* bboxes, cudaStream_t st);
 cudaError_t launch_single_segment(const uint8_t* img, int W, int H, int channels, const int64_t* labels,

@@ -33,21 +33,31 @@ cudaError_t launch_reward(const Tables& t, const EstParams& p, const double* ima
 }
 
 // ---- Rule P (src/image_slicer.cpp:59-66): masked bbox crop of one segment, u8 [h,w,4]
-__global__ void slice_kernel(Tables t, int v, int k, uint32_t* out, size_t cap_px) {
+template <typename LT>
+__global__ void slice_kernel(Tables t, Inputs in, int v, int k, uint32_t* out, size_t cap_px) {
     const int4 bb = t.bboxes[(int64_t)v * t.Kmax + k];
     const int w = bb.z - bb.x + 1, h = bb.w - bb.y + 1;
     if (w <= 0 || h <= 0) return;
-    const uint2* map = t.pixlab + (int64_t)v * t.H * t.W;
+    const int64_t HW = (int64_t)t.H * t.W;
+    const float* img = in.images + (int64_t)(v / in.S) * 3 * HW;
+    const LT* lab = static_cast<const LT*>(in.labels) + (int64_t)v * HW;
+    const LT key = (LT)t.keys[(int64_t)v * t.Kmax + k];
     const int64_t n = (int64_t)w * h;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n && (size_t)i < cap_px; i += (int64_t)gridDim.x * blockDim.x) {
         const int y = (int)(i / w), x = (int)(i - (int64_t)y * w);
-        const uint2 q = map[(int64_t)(bb.y + y) * t.W + bb.x + x];
-        out[i] = q.y == (uint32_t)k ? q.x : 0u;
+        const int64_t g = (int64_t)(bb.y + y) * t.W + bb.x + x;
+        uint32_t px = 0u;
+        if (lab[g] == key) {
+            auto tb = [](float f) { return (uint32_t)__float2int_rn(fminf(fmaxf(f, 0.f), 255.f)); };
+            px = tb(img[g]) | tb(img[HW + g]) << 8 | tb(img[2 * HW + g]) << 16 | 0xff000000u;
+        }
+        out[i] = px;
     }
 }
 
-cudaError_t launch_slice(const Tables& t, int v, int k, uint8_t* out, size_t cap, cudaStream_t st) {
-    slice_kernel<<<148, 256, 0, st>>>(t, v, k, reinterpret_cast<uint32_t*>(out), cap / 4);
+cudaError_t launch_slice(const Tables& t, const Inputs& in, int v, int k, uint8_t* out, size_t cap, cudaStream_t st) {
+    if (in.label_dtype == ICR_LABELS_I64) slice_kernel<int64_t><<<148, 256, 0, st>>>(t, in, v, k, reinterpret_cast<uint32_t*>(out), cap / 4);
+    else slice_kernel<int32_t><<<148, 256, 0, st>>>(t, in, v, k, reinterpret_cast<uint32_t*>(out), cap / 4);
     count_launch();
     return cudaGetLastError();
 }

@@ -115,12 +115,12 @@ class Workspace:
             out.append(t)
         return tuple(out)
 
-    def pixlab(self):
-        """[V,H,W,2] uint32 view copy: (RGBA bytes little-endian, compact id)."""
-        pp = C.c_void_p()
-        _check(lib().icr_workspace_tables(self._h, None, None, None, None, C.byref(pp), None))
-        t = torch.empty((self.V, self.H, self.W, 2), dtype=torch.int32, device=self.device)
-        _d2d(t, pp)
+    def keys(self):
+        """[V,Kmax] int64: original label value of each compact id (ascending within a map: Rule L)."""
+        pk = C.c_void_p()
+        _check(lib().icr_workspace_tables(self._h, None, None, None, None, C.byref(pk), None))
+        t = torch.empty((self.V, self.Kmax), dtype=torch.int64, device=self.device)
+        _d2d(t, pk)
         return t
 
     def debug_segment(self, v, k, h, params=None):
@@ -266,8 +266,9 @@ def estimate_png_size_masked_segment_to_output(img_hwc_u8, labels_compact_hw, co
     return (out, tabs) if debug else out
 
 
-def segment_stats(labels, Kmax=None, workspace=None):
-    """Batched Rule L + Rule S: labels [V,H,W] int32/int64 CUDA -> (K [V], counts [V,Kmax], bboxes [V,Kmax,4])."""
+def segment_stats(labels, Kmax=None, workspace=None, compact=False):
+    """Batched Rule L + Rule S: labels [V,H,W] int32/int64 CUDA -> (K [V], counts [V,Kmax], bboxes [V,Kmax,4])
+    (+ compact ids int32 [V,H,W], the inverse at::_unique would return, when compact=True)."""
     if not labels.is_cuda:
         raise RuntimeError("labels must be CUDA")
     V, H, W = labels.shape
@@ -275,12 +276,14 @@ def segment_stats(labels, Kmax=None, workspace=None):
         labels = labels.to(torch.int64)
     labels = labels.contiguous()
     ws = workspace or get_workspace(labels.device, V, H, W, Kmax)
+    comp = torch.empty((V, H, W), dtype=torch.int32, device=labels.device) if compact else None
     with torch.cuda.device(labels.device):
         _check(lib().icr_segment_stats(_ptr(labels), C.c_int(ICR_LABELS_I64 if labels.dtype == torch.int64 else ICR_LABELS_I32),
-                                       C.c_int(V), C.c_int(H), C.c_int(W), None, None, None, ws.handle, _stream()))
+                                       C.c_int(V), C.c_int(H), C.c_int(W), None, None, None,
+                                       _ptr(comp) if compact else None, ws.handle, _stream()))
         ws.check()
     K, counts, bboxes, _ = ws.tables()
-    return K[:V], counts[:V], bboxes[:V]
+    return (K[:V], counts[:V], bboxes[:V], comp) if compact else (K[:V], counts[:V], bboxes[:V])
 
 
 def labels_from_rama(node_labels_bn_i32, H, W):

@@ -85,9 +85,11 @@ int64_t icr_label_capacity(int H, int W);
 
 /* ---- segment_stats batched, with Rule L folded in (src/compute_rewards.cu:131-141 +
  * src/segment_stats.cu:11-77).  Fills the workspace tables and, when non-NULL, copies them out:
- * K_out int32 [V]; counts int32 [V,Kmax]; bboxes int32 [V,Kmax,4] = (x0,y0,x1,y1) inclusive. */
+ * K_out int32 [V]; counts int32 [V,Kmax]; bboxes int32 [V,Kmax,4] = (x0,y0,x1,y1) inclusive;
+ * compact_out int32 [V,H,W] = the compact ids at::_unique's inverse would hold (the batch path never
+ * materialises them: it masks by comparing raw labels with the segment's key). */
 int icr_segment_stats(const void* labels, int label_dtype, int V, int H, int W,
-                      int32_t* K_out, int32_t* counts, int32_t* bboxes,
+                      int32_t* K_out, int32_t* counts, int32_t* bboxes, int32_t* compact_out,
                       icr_workspace* ws, icr_stream stream);
 
 /* Pointer-level drop-in for compute_counts_bboxes_from_compact_labels_cuda
@@ -112,13 +114,13 @@ int icr_estimate_png_size_segment(const uint8_t* img_hwc_u8, int full_W, int ful
 
 /* ---- read-back of the tables the last icr_compute_rewards / icr_segment_stats left in the
  * workspace (device pointers, valid until the next call): K int32 [V], counts int32 [V,Kmax],
- * bboxes int32 [V,Kmax,4], seg_sizes f64 [V,Kmax], pixlab u32 [V,H,W,2] = (RGBA bytes, compact id). */
+ * bboxes int32 [V,Kmax,4], seg_sizes f64 [V,Kmax], keys i64 [V,Kmax] = original label of compact id k. */
 int icr_workspace_tables(icr_workspace* ws, const int32_t** K, const int32_t** counts,
-                         const int32_t** bboxes, const double** seg_sizes, const uint32_t** pixlab,
+                         const int32_t** bboxes, const double** seg_sizes, const long long** keys,
                          int* Kmax);
 
-/* Debug tables of ONE segment of the batch path (label map v, compact id k), produced by the
- * same device code the batch uses: row costs u32 [h*5], filter ids u8 [h], histogram u32 [4*256],
+/* Debug tables of ONE segment of the last batch call (label map v, compact id k; the caller's images and
+ * labels of that call must still be alive), produced by the same device code the batch uses: row costs u32 [h*5], filter ids u8 [h], histogram u32 [4*256],
  * match u64 [3] (device pointers, may be NULL). */
 int icr_debug_segment(icr_workspace* ws, int v, int k, const icr_params* params,
                       uint32_t* row_costs, uint8_t* filter_id, uint32_t* hist,

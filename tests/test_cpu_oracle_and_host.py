@@ -115,7 +115,7 @@ def test_c_abi_argument_errors_without_a_gpu(icr):
     assert b"null ptr" in L.icr_last_error()
     assert L.icr_estimate_png_size_segment(None, 8, 8, 4, None, None, 0, 0, 0, 8, 8, 1, 4, ctypes.c_float(0), ctypes.c_float(0),
                                            ctypes.c_float(0), ctypes.c_double(0), 1, None, None, None, None, None, None) == 1
-    assert L.icr_workspace_bytes(4, 224, 224, 64) > 4 * 224 * 224 * 8
+    assert 4 * 64 * 36 < L.icr_workspace_bytes(4, 224, 224, 64) < 1 << 20        # no per-pixel plane in the workspace
     assert L.icr_label_capacity(224, 224) == 65536 and L.icr_label_capacity(512, 512) == 512 * 512
     q = icr.IcrParams()
     L.icr_default_params(ctypes.byref(q))

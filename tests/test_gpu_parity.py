@@ -26,6 +26,7 @@ def _run(icr, dev, images, labels, sizes, Kmax=None, **kw):
     ws = icr.Workspace(dev, V, H, W, Kmax)
     ti, tl, ts = _to(dev, images, labels, sizes)
     r = icr.compute_rewards_batched(ti, tl, ts, workspace=ws, **kw)
+    ws.inputs = (ti, tl, ts)          # the debug/slice entries read the caller's buffers of the last call: keep them alive
     return r.cpu().numpy(), ws
 
 
@@ -47,14 +48,13 @@ def _check_batch(icr, orc, dev, images, labels, sizes, tables=True, n_debug=6, K
     assert _rel(got, want) < RTOL
     if not tables:
         return got, ws
-    # bytes and ids the estimator reads (Rule C, Rule L)
-    pl = ws.pixlab().cpu().numpy()
+    # Rule L: keys = sorted unique labels, compact ids = their ranks; Rule C/P bytes are checked through the slices below
+    keys = ws.keys().cpu().numpy()
     rng = np.random.default_rng(7)
     for b in range(min(B, 3)):
         rgba = orc.chw3_f32_to_rgba(images[b])
-        comp, _ = orc.compact_labels(labels[b])
-        assert np.array_equal(pl[b, :, :, 0].view(np.uint32), rgba.view(np.uint32)[:, :, 0]), "RGBA bytes"
-        assert np.array_equal(pl[b, :, :, 1], comp.astype(np.int32)), "compact ids"
+        comp, uniq = orc.compact_labels(labels[b])
+        assert np.array_equal(keys[b, :len(uniq)], uniq), "segment keys (sorted unique labels)"
         for k in rng.choice(det["K"][b], size=min(n_debug, det["K"][b]), replace=False):
             x0, y0, x1, y1 = det["bboxes"][b, k]
             w, h = x1 - x0 + 1, y1 - y0 + 1
@@ -74,6 +74,17 @@ def _check_batch(icr, orc, dev, images, labels, sizes, tables=True, n_debug=6, K
 
 def test_selftest_packed_arithmetic(icr, dev):
     assert icr.selftest() == 0
+
+
+def test_segment_stats_entry_with_compact_ids(icr, orc, dev):
+    labels = np.stack([synth.bfs_partition(60, 84, 9, seed=b) * 11 - 40 for b in range(3)]).astype(np.int64)
+    K, counts, bboxes, comp = icr.segment_stats(torch.from_numpy(labels).to(dev), compact=True)
+    for b in range(3):
+        want, uniq = orc.compact_labels(labels[b])
+        wc, wb = orc.segment_stats(want, len(uniq))
+        assert K[b].item() == len(uniq)
+        assert np.array_equal(comp[b].cpu().numpy(), want.astype(np.int32))
+        assert np.array_equal(counts[b, :len(uniq)].cpu().numpy(), wc) and np.array_equal(bboxes[b, :len(uniq)].cpu().numpy(), wb)
 
 
 def test_config2_rect_partitions(icr, orc, dev):
