@@ -47,16 +47,19 @@ __device__ __forceinline__ uint32_t to_byte(float v) {   // Rule C (src/compute_
     return (uint32_t)__float2int_rn(fminf(fmaxf(v, 0.f), 255.f));
 }
 
-template <typename LT>
+// FULL: the segment fills its bbox (count == w*h), so no label has to be read at all
+template <typename LT, bool FULL>
 __device__ __forceinline__ uint32_t masked_rgba(const float* __restrict__ img, const LT* __restrict__ lab,
                                                 int64_t HW, int64_t idx, LT key) {
-    if (__ldg(lab + idx) != key) return 0u;
+    // all four loads are issued together; the mask is applied afterwards (one memory round trip, not two)
     const float r = __ldg(img + idx), g = __ldg(img + HW + idx), b = __ldg(img + 2 * HW + idx);
-    return to_byte(r) | to_byte(g) << 8 | to_byte(b) << 16 | 0xff000000u;
+    const uint32_t px = to_byte(r) | to_byte(g) << 8 | to_byte(b) << 16 | 0xff000000u;
+    if (FULL) return px;
+    return __ldg(lab + idx) == key ? px : 0u;
 }
 
 template <typename LT, bool DEBUG>
-__device__ void warp_segment(const float* __restrict__ img, const LT* __restrict__ lab, int64_t HW, int W, LT key,
+__device__ void warp_segment(const float* __restrict__ img, const LT* __restrict__ lab, int64_t HW, int W, LT key, int count,
                              int4 bb, uint32_t* hist, uint32_t* tile, const EstParams& p,
                              const double* __restrict__ clog2, double* out, const DebugOut& dbg) {
     const int lane = threadIdx.x & 31;
@@ -89,6 +92,7 @@ __device__ void warp_segment(const float* __restrict__ img, const LT* __restrict
     for (int s = lane; s <= R; s += 32) tile[s * stride] = 0u;
     for (int x = lane; x < stride + 8; x += 32) tile[x] = 0u;
     int s0 = 1;                                          // slot of the group's first row; row y lives in slot (y+1) mod (R+1)
+    const bool full = count == w * h;
     const float* imgp = img + (int64_t)bb.y * W + bb.x;
     const LT* labp = lab + (int64_t)bb.y * W + bb.x;
 
@@ -101,7 +105,8 @@ __device__ void warp_segment(const float* __restrict__ img, const LT* __restrict
                 int slot = s0 + rr; if (slot > R) slot -= R + 1;
                 uint32_t* trow = tile + slot * stride + 1;
                 const int64_t rowoff = (int64_t)yy * W;
-                for (int x = tx; x < w; x += (1 << twl)) trow[x] = masked_rgba<LT>(imgp, labp, HW, rowoff + x, key);
+                if (full) { for (int x = tx; x < w; x += (1 << twl)) trow[x] = masked_rgba<LT, true>(imgp, labp, HW, rowoff + x, key); }
+                else { for (int x = tx; x < w; x += (1 << twl)) trow[x] = masked_rgba<LT, false>(imgp, labp, HW, rowoff + x, key); }
             }
         }
         __syncwarp();
@@ -244,7 +249,8 @@ __global__ void __launch_bounds__(EST_WARPS * 32) estimate_kernel(Tables t, Inpu
             const int4 bb = __ldg(t.bboxes + (int64_t)v * t.Kmax + k);
             if (for_big_kernel(bb.z - bb.x + 1, bb.w - bb.y + 1, p.L_min)) continue;
             const LT key = (LT)__ldg(t.keys + (int64_t)v * t.Kmax + k);
-            warp_segment<LT, false>(in.images + (int64_t)(v / in.S) * 3 * HW, labels + (int64_t)v * HW, HW, t.W, key, bb,
+            warp_segment<LT, false>(in.images + (int64_t)(v / in.S) * 3 * HW, labels + (int64_t)v * HW, HW, t.W, key,
+                                    __ldg(t.counts + (int64_t)v * t.Kmax + k), bb,
                                     hist, tile_all[warp], p, t.clog2, t.seg_sizes + (int64_t)v * t.Kmax + k, none);
         }
     }
@@ -262,7 +268,8 @@ __global__ void __launch_bounds__(32) estimate_debug_kernel(Tables t, Inputs in,
     const LT key = (LT)t.keys[(int64_t)dbg.v * t.Kmax + dbg.k];
     double scratch;
     warp_segment<LT, true>(in.images + (int64_t)(dbg.v / in.S) * 3 * HW, static_cast<const LT*>(in.labels) + (int64_t)dbg.v * HW,
-                           HW, t.W, key, bb, hist, tile, p, t.clog2, dbg.size ? dbg.size : &scratch, dbg);
+                           HW, t.W, key, t.counts[(int64_t)dbg.v * t.Kmax + dbg.k], bb, hist, tile, p, t.clog2,
+                           dbg.size ? dbg.size : &scratch, dbg);
 }
 
 static int est_grid() {
