@@ -28,8 +28,11 @@ struct DebugOut {
     uint32_t* row_costs; uint8_t* filter_id; uint32_t* hist; unsigned long long* match; double* size;
 };
 
+// c*log2(c): table for the counts that occur in practice, one out-of-line copy of the slow path (log2 in double is
+// ~100 instructions; inlined at every use it blew the kernel up to 96 KB and the warps stalled on instruction fetch)
+__device__ __noinline__ double clog2_slow(uint32_t c) { return (double)c * log2((double)c); }
 __device__ __forceinline__ double clog2_of(uint32_t c, const double* __restrict__ tab) {
-    return c < (uint32_t)CLOG2_N ? __ldg(tab + c) : (double)c * log2((double)c);
+    return c < (uint32_t)CLOG2_N ? __ldg(tab + c) : clog2_slow(c);
 }
 
 // Rule Z (src/png_size_estimator.cu:10-28), every operand widened to double as at :588
@@ -58,13 +61,46 @@ __device__ __forceinline__ uint32_t masked_rgba(const float* __restrict__ img, c
     return __ldg(lab + idx) == key ? px : 0u;
 }
 
-template <typename LT, bool DEBUG>
+// ---- asynchronous row staging: one bulk copy (TMA, no tensor map) per bbox row and plane, completion on an mbarrier
+constexpr int RAW_PX = 384;           // max over geometries of R * (16-byte aligned row width)
+
+template <typename LT>
+struct __align__(16) WarpSmem {
+    uint32_t hist[1024];              // 4 x 256 residual histogram
+    float raw[3 * RAW_PX];            // R rows x wa pixels of the three f32 planes, as delivered
+    LT rawlab[RAW_PX];                // and of the label plane
+    uint32_t tile[TILE_WORDS];        // masked RGBA words, (R+1) rolling row slots
+    unsigned long long mbar;
+};
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long* m, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(m)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long* m, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(m)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* m, uint32_t parity) {
+    asm volatile(
+        "{\n.reg .pred p;\nWAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\nbra WAIT_%=;\nDONE_%=:\n}" ::"r"(smem_u32(m)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, unsigned long long* m) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(m)) : "memory");
+}
+
+// BULK: rows arrive through bulk copies (needs W % 4 == 0 and 16-byte aligned planes); otherwise plain loads.
+template <typename LT, bool DEBUG, bool BULK>
 __device__ void warp_segment(const float* __restrict__ img, const LT* __restrict__ lab, int64_t HW, int W, LT key, int count,
-                             int4 bb, uint32_t* hist, uint32_t* tile, const EstParams& p,
+                             int4 bb, WarpSmem<LT>& sm, uint32_t& phase, const EstParams& p,
                              const double* __restrict__ clog2, double* out, const DebugOut& dbg) {
     const int lane = threadIdx.x & 31;
     const int w = bb.z - bb.x + 1, h = bb.w - bb.y + 1;
     if (w <= 0 || h <= 0) { if (lane == 0) *out = 0.0; return; }   // src/compute_rewards.cu:164
+    uint32_t* hist = sm.hist;
+    uint32_t* tile = sm.tile;
 
     // strips per row S = 2^lg with strip width sw <= 8; among those minimise (row groups) x (strip width + fixed cost)
     int lg = 0;
@@ -83,33 +119,63 @@ __device__ void warp_segment(const float* __restrict__ img, const LT* __restrict
     const int xs = stp * sw;
     const int nstrip = max(0, min(sw, w - xs));
     const int stride = (S * sw + 1) | 1;                 // guard column + row, odd so rows land on different banks
-    // staging geometry: lanes along x, tw = power of two covering min(w, 32)
+    // conversion geometry: lanes along x, tw = power of two covering min(w, 32)
     int twl = 0;
     while ((1 << twl) < w && twl < 5) ++twl;
     const int tx = lane & ((1 << twl) - 1), ty = lane >> twl, rpp = 32 >> twl;
+    const bool full = count == w * h;                    // the segment fills its bbox: no label has to be read
+    // bulk-copy geometry: rows widened to 16-byte boundaries
+    const int x0a = bb.x & ~3, wa = ((bb.x + w + 3) & ~3) - x0a, dx = bb.x - x0a;
+    const float* imgp = img + (int64_t)bb.y * W + (BULK ? x0a : bb.x);
+    const LT* labp = lab + (int64_t)bb.y * W + (BULK ? x0a : bb.x);
+
+    auto issue = [&](int yb) {
+        const int nrows = min(R, h - yb);
+        if (lane == 0) mbar_expect_tx(&sm.mbar, (uint32_t)nrows * (uint32_t)wa * (12u + (full ? 0u : (uint32_t)sizeof(LT))));
+        __syncwarp();
+        if (lane < nrows) {
+            const int64_t off = (int64_t)(yb + lane) * W;
+            bulk_g2s(sm.raw + (0 * R + lane) * wa, imgp + off, wa * 4, &sm.mbar);
+            bulk_g2s(sm.raw + (1 * R + lane) * wa, imgp + HW + off, wa * 4, &sm.mbar);
+            bulk_g2s(sm.raw + (2 * R + lane) * wa, imgp + 2 * HW + off, wa * 4, &sm.mbar);
+            if (!full) bulk_g2s(sm.rawlab + lane * wa, labp + off, wa * (int)sizeof(LT), &sm.mbar);
+        }
+    };
 
     // zero the guard column of every slot and the slot of row -1
     for (int s = lane; s <= R; s += 32) tile[s * stride] = 0u;
     for (int x = lane; x < stride + 8; x += 32) tile[x] = 0u;
     int s0 = 1;                                          // slot of the group's first row; row y lives in slot (y+1) mod (R+1)
-    const bool full = count == w * h;
-    const float* imgp = img + (int64_t)bb.y * W + bb.x;
-    const LT* labp = lab + (int64_t)bb.y * W + bb.x;
+    if (BULK) issue(0);
 
     for (int yb = 0; yb < h; yb += R) {
         __syncwarp();
-        // ---- stage rows yb .. yb+R-1 (coalesced along x), masked and packed
+        // ---- rows yb .. yb+R-1 -> masked, packed RGBA words in the tile (lanes along x)
+        if (BULK) { mbar_wait(&sm.mbar, phase); phase ^= 1u; }
         for (int r0 = 0; r0 < R; r0 += rpp) {
             const int rr = r0 + ty, yy = yb + rr;
             if (rr < R && yy < h) {
                 int slot = s0 + rr; if (slot > R) slot -= R + 1;
                 uint32_t* trow = tile + slot * stride + 1;
-                const int64_t rowoff = (int64_t)yy * W;
-                if (full) { for (int x = tx; x < w; x += (1 << twl)) trow[x] = masked_rgba<LT, true>(imgp, labp, HW, rowoff + x, key); }
-                else { for (int x = tx; x < w; x += (1 << twl)) trow[x] = masked_rgba<LT, false>(imgp, labp, HW, rowoff + x, key); }
+                if (BULK) {
+                    const float* r0p = sm.raw + rr * wa + dx;
+                    const LT* l0p = sm.rawlab + rr * wa + dx;
+                    for (int x = tx; x < w; x += (1 << twl)) {
+                        const uint32_t px = to_byte(r0p[x]) | to_byte(r0p[R * wa + x]) << 8 | to_byte(r0p[2 * R * wa + x]) << 16 | 0xff000000u;
+                        trow[x] = (full || l0p[x] == key) ? px : 0u;
+                    }
+                } else {
+                    const int64_t rowoff = (int64_t)yy * W;
+                    if (full) { for (int x = tx; x < w; x += (1 << twl)) trow[x] = masked_rgba<LT, true>(imgp, labp, HW, rowoff + x, key); }
+                    else { for (int x = tx; x < w; x += (1 << twl)) trow[x] = masked_rgba<LT, false>(imgp, labp, HW, rowoff + x, key); }
+                }
             }
         }
         __syncwarp();
+        if (BULK && yb + R < h) {                        // the raw rows are consumed: fetch the next group while this one is computed
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            issue(yb + R);
+        }
         // ---- lane = (row sr of the group, strip stp)
         const int y = yb + sr;
         const int n = y < h ? nstrip : 0;
@@ -183,7 +249,7 @@ __device__ void warp_segment(const float* __restrict__ img, const LT* __restrict
     double acc = 0.0;
     uint32_t nz = 0;
     uint4* h4 = reinterpret_cast<uint4*>(hist) + lane * 8;
-#pragma unroll
+#pragma unroll 1
     for (int j = 0; j < 8; ++j) {
         uint4 q = h4[j];
         if (DEBUG && dbg.hist) {
@@ -205,7 +271,7 @@ __device__ void warp_segment(const float* __restrict__ img, const LT* __restrict
     const uint32_t zeros = npx - nz;
     if (zeros) acc += clog2_of(zeros, clog2);
     if (DEBUG && dbg.hist) { __syncwarp(); if ((lane & 7) == 0) dbg.hist[(lane >> 3) * 256] = zeros; }
-    const double Hc = log2((double)npx) - acc / (double)npx;
+    const double Hc = clog2_of(npx, clog2) / (double)npx - acc / (double)npx;       // log2(n) = (n log2 n)/n
     const double H0 = __shfl_sync(0xffffffffu, Hc, 0), H1 = __shfl_sync(0xffffffffu, Hc, 8);
     const double H2 = __shfl_sync(0xffffffffu, Hc, 16), H3 = __shfl_sync(0xffffffffu, Hc, 24);
     if (lane == 0) {
@@ -219,14 +285,16 @@ __device__ void warp_segment(const float* __restrict__ img, const LT* __restrict
     }
 }
 
-template <typename LT>
+template <typename LT, bool BULK>
 __global__ void __launch_bounds__(EST_WARPS * 32) estimate_kernel(Tables t, Inputs in, EstParams p) {
-    __shared__ __align__(16) uint32_t hist_all[EST_WARPS][1024];
-    __shared__ uint32_t tile_all[EST_WARPS][TILE_WORDS];
+    extern __shared__ __align__(16) unsigned char est_smem[];
+    WarpSmem<LT>* wsm = reinterpret_cast<WarpSmem<LT>*>(est_smem);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    uint32_t* hist = hist_all[warp];
-    for (int i = lane; i < 1024; i += 32) hist[i] = 0;
+    WarpSmem<LT>& sm = wsm[warp];
+    for (int i = lane; i < 1024; i += 32) sm.hist[i] = 0;
+    if (lane == 0) { mbar_init(&sm.mbar, 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
     __syncwarp();
+    uint32_t phase = 0;
     const int64_t HW = (int64_t)t.H * t.W;
     const int total = t.seg_prefix[t.V];
     const LT* labels = static_cast<const LT*>(in.labels);
@@ -249,48 +317,66 @@ __global__ void __launch_bounds__(EST_WARPS * 32) estimate_kernel(Tables t, Inpu
             const int4 bb = __ldg(t.bboxes + (int64_t)v * t.Kmax + k);
             if (for_big_kernel(bb.z - bb.x + 1, bb.w - bb.y + 1, p.L_min)) continue;
             const LT key = (LT)__ldg(t.keys + (int64_t)v * t.Kmax + k);
-            warp_segment<LT, false>(in.images + (int64_t)(v / in.S) * 3 * HW, labels + (int64_t)v * HW, HW, t.W, key,
-                                    __ldg(t.counts + (int64_t)v * t.Kmax + k), bb,
-                                    hist, tile_all[warp], p, t.clog2, t.seg_sizes + (int64_t)v * t.Kmax + k, none);
+            warp_segment<LT, false, BULK>(in.images + (int64_t)(v / in.S) * 3 * HW, labels + (int64_t)v * HW, HW, t.W, key,
+                                          __ldg(t.counts + (int64_t)v * t.Kmax + k), bb, sm, phase, p, t.clog2,
+                                          t.seg_sizes + (int64_t)v * t.Kmax + k, none);
         }
     }
 }
 
-template <typename LT>
+template <typename LT, bool BULK>
 __global__ void __launch_bounds__(32) estimate_debug_kernel(Tables t, Inputs in, EstParams p, DebugOut dbg) {
-    __shared__ __align__(16) uint32_t hist[1024];
-    __shared__ uint32_t tile[TILE_WORDS];
-    for (int i = threadIdx.x; i < 1024; i += 32) hist[i] = 0;
+    extern __shared__ __align__(16) unsigned char est_smem[];
+    WarpSmem<LT>& sm = *reinterpret_cast<WarpSmem<LT>*>(est_smem);
+    for (int i = threadIdx.x; i < 1024; i += 32) sm.hist[i] = 0;
+    if (threadIdx.x == 0) { mbar_init(&sm.mbar, 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
     __syncwarp();
+    uint32_t phase = 0;
     const int64_t HW = (int64_t)t.H * t.W;
     const int4 bb = t.bboxes[(int64_t)dbg.v * t.Kmax + dbg.k];
     if (for_big_kernel(bb.z - bb.x + 1, bb.w - bb.y + 1, p.L_min)) return;     // the big-segment debug kernel acts
     const LT key = (LT)t.keys[(int64_t)dbg.v * t.Kmax + dbg.k];
     double scratch;
-    warp_segment<LT, true>(in.images + (int64_t)(dbg.v / in.S) * 3 * HW, static_cast<const LT*>(in.labels) + (int64_t)dbg.v * HW,
-                           HW, t.W, key, t.counts[(int64_t)dbg.v * t.Kmax + dbg.k], bb, hist, tile, p, t.clog2,
-                           dbg.size ? dbg.size : &scratch, dbg);
+    warp_segment<LT, true, BULK>(in.images + (int64_t)(dbg.v / in.S) * 3 * HW, static_cast<const LT*>(in.labels) + (int64_t)dbg.v * HW,
+                                 HW, t.W, key, t.counts[(int64_t)dbg.v * t.Kmax + dbg.k], bb, sm, phase, p, t.clog2,
+                                 dbg.size ? dbg.size : &scratch, dbg);
 }
 
-static int est_grid() {
-    static int g = 0;
-    if (!g) {
-        int dev = 0, sms = 148, a = 0, b = 0;
+static bool bulk_ok(const Tables& t, const Inputs& in) {
+    return t.W % 4 == 0 && (uintptr_t)in.images % 16 == 0 && (uintptr_t)in.labels % 16 == 0;
+}
+
+template <typename LT, bool BULK>
+static cudaError_t launch_est_t(const Tables& t, const Inputs& in, const EstParams& p, cudaStream_t st) {
+    static int grid = 0;
+    const size_t smem = sizeof(WarpSmem<LT>) * EST_WARPS;
+    auto kern = estimate_kernel<LT, BULK>;
+    if (!grid) {
+        int dev = 0, sms = 148, per = 0;
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&a, estimate_kernel<int32_t>, EST_WARPS * 32, 0);
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, estimate_kernel<int64_t>, EST_WARPS * 32, 0);
-        int per = a < b ? a : b;
-        if (per < 1) per = 1;
-        g = sms * per;
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, kern, EST_WARPS * 32, smem);
+        grid = sms * (per < 1 ? 1 : per);     // persistent: every CTA resident, warps pull work until the list is empty
     }
-    return g;
+    kern<<<grid, EST_WARPS * 32, smem, st>>>(t, in, p);
+    count_launch();
+    return cudaGetLastError();
 }
 
 cudaError_t launch_estimate(const Tables& t, const Inputs& in, const EstParams& p, cudaStream_t st) {
-    const int grid = est_grid();     // persistent: every CTA resident, warps pull work until the list is empty
-    if (in.label_dtype == ICR_LABELS_I64) estimate_kernel<int64_t><<<grid, EST_WARPS * 32, 0, st>>>(t, in, p);
-    else estimate_kernel<int32_t><<<grid, EST_WARPS * 32, 0, st>>>(t, in, p);
+    const bool bulk = bulk_ok(t, in);
+    if (in.label_dtype == ICR_LABELS_I64) return bulk ? launch_est_t<int64_t, true>(t, in, p, st) : launch_est_t<int64_t, false>(t, in, p, st);
+    return bulk ? launch_est_t<int32_t, true>(t, in, p, st) : launch_est_t<int32_t, false>(t, in, p, st);
+}
+
+template <typename LT, bool BULK>
+static cudaError_t launch_dbg_t(const Tables& t, const Inputs& in, const EstParams& p, const DebugOut& d, cudaStream_t st) {
+    auto kern = estimate_debug_kernel<LT, BULK>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(WarpSmem<LT>));
+    if (e != cudaSuccess) return e;
+    kern<<<1, 32, sizeof(WarpSmem<LT>), st>>>(t, in, p, d);
     count_launch();
     return cudaGetLastError();
 }
@@ -299,10 +385,9 @@ cudaError_t launch_estimate_debug(const Tables& t, const Inputs& in, const EstPa
                                   uint8_t* filter_id, uint32_t* hist, unsigned long long* match, double* size_out,
                                   cudaStream_t st) {
     DebugOut d{v, k, row_costs, filter_id, hist, match, size_out};
-    if (in.label_dtype == ICR_LABELS_I64) estimate_debug_kernel<int64_t><<<1, 32, 0, st>>>(t, in, p, d);
-    else estimate_debug_kernel<int32_t><<<1, 32, 0, st>>>(t, in, p, d);
-    count_launch();
-    return cudaGetLastError();
+    const bool bulk = bulk_ok(t, in);
+    if (in.label_dtype == ICR_LABELS_I64) return bulk ? launch_dbg_t<int64_t, true>(t, in, p, d, st) : launch_dbg_t<int64_t, false>(t, in, p, d, st);
+    return bulk ? launch_dbg_t<int32_t, true>(t, in, p, d, st) : launch_dbg_t<int32_t, false>(t, in, p, d, st);
 }
 
 }  // namespace icr
