@@ -9,12 +9,23 @@
 namespace icr {
 
 // sum over the 4 bytes of |int8(d)| + acc, where d holds |cur-pred| per byte (0..255).
-// |int8(r)| is symmetric in r -> -r, so the wrapped residual and |cur-pred| cost the same;
-// x^0x80 maps a byte to offset-binary, whose distance to 0x80 is |int8(x)|.
+// |int8(r)| is symmetric in r -> -r, so the wrapped residual and |cur-pred| cost the same; with signed byte
+// operands VABSDIFF4 against zero is exactly |int8(d)| (d = 128 gives 128), accumulated in the same instruction.
 __device__ __forceinline__ uint32_t cost_acc(uint32_t d, uint32_t acc) {
     uint32_t r;
-    asm("vabsdiff4.u32.u32.u32.add %0, %1, %2, %3;" : "=r"(r) : "r"(d ^ 0x80808080u), "r"(0x80808080u), "r"(acc));
+    asm("vabsdiff4.u32.s32.s32.add %0, %1, %2, %3;" : "=r"(r) : "r"(d), "r"(0u), "r"(acc));
     return r;
+}
+
+// Rule C (src/compute_rewards.cu:15-20): clamp to [0,255] and round half to even.  A float -> u8 conversion
+// saturates to the destination range and maps NaN to 0, which is what fminf(fmaxf(v,0),255) + lrintf produce.
+__device__ __forceinline__ uint32_t byte_of(float v) {
+    uint32_t r;
+    asm("cvt.rni.u8.f32 %0, %1;" : "=r"(r) : "f"(v));
+    return r;
+}
+__device__ __forceinline__ uint32_t rgba_of(float r, float g, float b) {
+    return byte_of(r) | byte_of(g) << 8 | byte_of(b) << 16 | 0xff000000u;
 }
 
 __device__ __forceinline__ uint32_t absdiff4(uint32_t a, uint32_t b) { return __vabsdiffu4(a, b); }
