@@ -82,6 +82,13 @@ __device__ __forceinline__ int choose_geometry(int w, int h) {
     return lg;
 }
 
+// hist[C][b] += 1 unless b == 0: one predicated shared-memory reduction, no branch
+template <int C>
+__device__ __forceinline__ void hist_add(uint32_t hist_s, uint32_t b) {
+    asm volatile("{\n.reg .pred p;\nsetp.ne.u32 p, %1, 0;\n@p red.shared.add.u32 [%0+%2], 1;\n}"
+                 :: "r"(hist_s + 4u * b), "r"(b), "n"(C * 1024) : "memory");
+}
+
 // ---- stage rows yb .. yb+nr-1 of the bbox into the tile: lanes take the nr*w pixels in row-major order
 template <typename LT, bool FULL>
 __device__ __forceinline__ void stage_rows(const float* __restrict__ img, const LT* __restrict__ lab, int64_t HW, int W, LT key,
@@ -117,8 +124,57 @@ __device__ __forceinline__ void stage_rows(const float* __restrict__ img, const 
     }
 }
 
+// Same, 4 pixels per lane and load: rows are widened to 16-byte boundaries [x0a, x0a + 4*nq) and fetched as float4 / int4
+// quads (needs W % 4 == 0 and 16-byte aligned planes); pixels of a quad that fall outside the bbox are dropped.
+__device__ __forceinline__ void load_quad(const int32_t* p, int32_t (&l)[4]) {
+    const int4 q = __ldg(reinterpret_cast<const int4*>(p));
+    l[0] = q.x; l[1] = q.y; l[2] = q.z; l[3] = q.w;
+}
+__device__ __forceinline__ void load_quad(const int64_t* p, int64_t (&l)[4]) {
+    const longlong2 a = __ldg(reinterpret_cast<const longlong2*>(p)), b = __ldg(reinterpret_cast<const longlong2*>(p + 2));
+    l[0] = a.x; l[1] = a.y; l[2] = b.x; l[3] = b.y;
+}
+
+template <typename LT, bool FULL>
+__device__ __forceinline__ void stage_rows_vec(const float* __restrict__ img, const LT* __restrict__ lab, int64_t HW, int W, LT key,
+                                               int w, int dx, int nq, float rnq, int nr, int s0, int R, int tst, uint32_t* tile, int lane) {
+    const int total = nr * nq;
+    constexpr int U = 2;                              // quads in flight per lane
+    for (int q0 = lane; q0 < total; q0 += 32 * U) {
+        float4 r[U], g[U], b[U];
+        LT l[U][4];
+        int dst[U], xb[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int q = q0 + 32 * u;
+            const int rr = __float2int_rz(((float)q + 0.5f) * rnq);       // q / nq, exact for q < 32*64 (see stage_rows)
+            const int xq = q - rr * nq;
+            int slot = s0 + rr; if (slot > R) slot -= R + 1;
+            xb[u] = q < total ? 4 * xq - dx : w;      // bbox column of the quad's first pixel; w = nothing to store
+            dst[u] = slot * tst + 1 + xb[u];
+            const int off = rr * W + 4 * xq;
+            if (q < total) {
+                r[u] = __ldg(reinterpret_cast<const float4*>(img + off));
+                g[u] = __ldg(reinterpret_cast<const float4*>(img + HW + off));
+                b[u] = __ldg(reinterpret_cast<const float4*>(img + 2 * HW + off));
+                if (!FULL) load_quad(lab + off, l[u]);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            if (xb[u] < w) {
+                const uint32_t px[4] = {rgba_of(r[u].x, g[u].x, b[u].x), rgba_of(r[u].y, g[u].y, b[u].y),
+                                        rgba_of(r[u].z, g[u].z, b[u].z), rgba_of(r[u].w, g[u].w, b[u].w)};
+#pragma unroll
+                for (int e = 0; e < 4; ++e)
+                    if ((unsigned)(xb[u] + e) < (unsigned)w) tile[dst[u] + e] = (FULL || l[u][e] == key) ? px[e] : 0u;
+            }
+        }
+    }
+}
+
 // One segment, one warp.  img/lab point at the image planes / label plane of the segment's map.
-template <typename LT, bool DEBUG>
+template <typename LT, bool DEBUG, bool VEC>
 __device__ void warp_segment(const float* __restrict__ img, const LT* __restrict__ lab, int64_t HW, int W, LT key, int count,
                              int4 bb, WarpSmem& sm, const EstParams& p, const double* __restrict__ clog2, double* out,
                              const DebugOut& dbg) {
@@ -127,6 +183,7 @@ __device__ void warp_segment(const float* __restrict__ img, const LT* __restrict
     if (w <= 0 || h <= 0) { if (lane == 0) *out = 0.0; return; }   // src/compute_rewards.cu:164
     uint32_t* hist = sm.hist;
     uint32_t* tile = sm.tile;
+    const uint32_t hist_s = (uint32_t)__cvta_generic_to_shared(hist);
 
     const int lg = choose_geometry(w, h);
     const int S = 1 << lg, R = 32 >> lg;
@@ -140,6 +197,9 @@ __device__ void warp_segment(const float* __restrict__ img, const LT* __restrict
     const float rw = 1.0f / (float)w;
     const float* imgp = img + (int64_t)bb.y * W + bb.x;
     const LT* labp = lab + (int64_t)bb.y * W + bb.x;
+    // quad staging: rows widened to 16-byte boundaries
+    const int x0a = bb.x & ~3, dx = bb.x - x0a, nq = (dx + w + 3) >> 2;
+    const float rnq = 1.0f / (float)nq;
 
     // zero the guard column of every slot and the slot of row -1
     for (int s = lane; s <= R; s += 32) tile[s * tst] = 0u;
@@ -149,8 +209,15 @@ __device__ void warp_segment(const float* __restrict__ img, const LT* __restrict
     for (int yb = 0; yb < h; yb += R) {
         __syncwarp();                                    // the previous group's walks are done with the slots about to be rewritten
         const int nr = min(R, h - yb);
-        if (full) stage_rows<LT, true>(imgp + (int64_t)yb * W, labp + (int64_t)yb * W, HW, W, key, w, rw, nr, s0, R, tst, tile, lane);
-        else stage_rows<LT, false>(imgp + (int64_t)yb * W, labp + (int64_t)yb * W, HW, W, key, w, rw, nr, s0, R, tst, tile, lane);
+        if (VEC) {
+            const float* ip = imgp + (int64_t)yb * W - dx;
+            const LT* lp = labp + (int64_t)yb * W - dx;
+            if (full) stage_rows_vec<LT, true>(ip, lp, HW, W, key, w, dx, nq, rnq, nr, s0, R, tst, tile, lane);
+            else stage_rows_vec<LT, false>(ip, lp, HW, W, key, w, dx, nq, rnq, nr, s0, R, tst, tile, lane);
+        } else {
+            if (full) stage_rows<LT, true>(imgp + (int64_t)yb * W, labp + (int64_t)yb * W, HW, W, key, w, rw, nr, s0, R, tst, tile, lane);
+            else stage_rows<LT, false>(imgp + (int64_t)yb * W, labp + (int64_t)yb * W, HW, W, key, w, rw, nr, s0, R, tst, tile, lane);
+        }
         __syncwarp();
 
         // ---- lane = (row sr of the group, strip stp)
@@ -211,13 +278,10 @@ __device__ void warp_segment(const float* __restrict__ img, const LT* __restrict
             for (int i = 0; i < n; ++i) {
                 const uint32_t r = __vsub4(trow[i], *pred);
                 pred += step;
-                if (r) {
-                    const uint32_t b0 = __byte_perm(r, 0, 0x4440), b1 = __byte_perm(r, 0, 0x4441), b2 = __byte_perm(r, 0, 0x4442), b3 = r >> 24;
-                    if (b0) atomicAdd(hist + b0, 1u);
-                    if (b1) atomicAdd(hist + 256 + b1, 1u);
-                    if (b2) atomicAdd(hist + 512 + b2, 1u);
-                    if (b3) atomicAdd(hist + 768 + b3, 1u);
-                }
+                hist_add<0>(hist_s, __byte_perm(r, 0, 0x4440));
+                hist_add<1>(hist_s, __byte_perm(r, 0, 0x4441));
+                hist_add<2>(hist_s, __byte_perm(r, 0, 0x4442));
+                hist_add<3>(hist_s, r >> 24);
             }
         }
         s0 = s0 == 0 ? R : s0 - 1;                       // (yb + R + 1) mod (R+1)
@@ -265,7 +329,7 @@ __device__ void warp_segment(const float* __restrict__ img, const LT* __restrict
     }
 }
 
-template <typename LT>
+template <typename LT, bool VEC>
 __global__ void __launch_bounds__(EST_WARPS * 32) estimate_kernel(Tables t, Inputs in, EstParams p) {
     extern __shared__ __align__(16) unsigned char est_smem[];
     WarpSmem* wsm = reinterpret_cast<WarpSmem*>(est_smem);
@@ -295,14 +359,14 @@ __global__ void __launch_bounds__(EST_WARPS * 32) estimate_kernel(Tables t, Inpu
             const int4 bb = __ldg(t.bboxes + (int64_t)v * t.Kmax + k);
             if (for_big_kernel(bb.z - bb.x + 1, bb.w - bb.y + 1, p.L_min)) continue;
             const LT key = (LT)__ldg(t.keys + (int64_t)v * t.Kmax + k);
-            warp_segment<LT, false>(in.images + (int64_t)(v / in.S) * 3 * HW, labels + (int64_t)v * HW, HW, t.W, key,
+            warp_segment<LT, false, VEC>(in.images + (int64_t)(v / in.S) * 3 * HW, labels + (int64_t)v * HW, HW, t.W, key,
                                     __ldg(t.counts + (int64_t)v * t.Kmax + k), bb, sm, p, t.clog2,
                                     t.seg_sizes + (int64_t)v * t.Kmax + k, none);
         }
     }
 }
 
-template <typename LT>
+template <typename LT, bool VEC>
 __global__ void __launch_bounds__(32) estimate_debug_kernel(Tables t, Inputs in, EstParams p, DebugOut dbg) {
     extern __shared__ __align__(16) unsigned char est_smem[];
     WarpSmem& sm = *reinterpret_cast<WarpSmem*>(est_smem);
@@ -313,16 +377,21 @@ __global__ void __launch_bounds__(32) estimate_debug_kernel(Tables t, Inputs in,
     if (for_big_kernel(bb.z - bb.x + 1, bb.w - bb.y + 1, p.L_min)) return;     // the big-segment debug kernel acts
     const LT key = (LT)t.keys[(int64_t)dbg.v * t.Kmax + dbg.k];
     double scratch;
-    warp_segment<LT, true>(in.images + (int64_t)(dbg.v / in.S) * 3 * HW, static_cast<const LT*>(in.labels) + (int64_t)dbg.v * HW,
+    warp_segment<LT, true, VEC>(in.images + (int64_t)(dbg.v / in.S) * 3 * HW, static_cast<const LT*>(in.labels) + (int64_t)dbg.v * HW,
                            HW, t.W, key, t.counts[(int64_t)dbg.v * t.Kmax + dbg.k], bb, sm, p, t.clog2,
                            dbg.size ? dbg.size : &scratch, dbg);
 }
 
-template <typename LT>
+// quad staging needs 16-byte aligned rows in every plane
+static bool vec_ok(const Tables& t, const Inputs& in) {
+    return t.W % 4 == 0 && (uintptr_t)in.images % 16 == 0 && (uintptr_t)in.labels % 16 == 0;
+}
+
+template <typename LT, bool VEC>
 static cudaError_t launch_est_t(const Tables& t, const Inputs& in, const EstParams& p, cudaStream_t st) {
     static int grid = 0;
     const size_t smem = sizeof(WarpSmem) * EST_WARPS;
-    auto kern = estimate_kernel<LT>;
+    auto kern = estimate_kernel<LT, VEC>;
     if (!grid) {
         int dev = 0, sms = 148, per = 0;
         cudaGetDevice(&dev);
@@ -338,13 +407,14 @@ static cudaError_t launch_est_t(const Tables& t, const Inputs& in, const EstPara
 }
 
 cudaError_t launch_estimate(const Tables& t, const Inputs& in, const EstParams& p, cudaStream_t st) {
-    if (in.label_dtype == ICR_LABELS_I64) return launch_est_t<int64_t>(t, in, p, st);
-    return launch_est_t<int32_t>(t, in, p, st);
+    const bool vec = vec_ok(t, in);
+    if (in.label_dtype == ICR_LABELS_I64) return vec ? launch_est_t<int64_t, true>(t, in, p, st) : launch_est_t<int64_t, false>(t, in, p, st);
+    return vec ? launch_est_t<int32_t, true>(t, in, p, st) : launch_est_t<int32_t, false>(t, in, p, st);
 }
 
-template <typename LT>
+template <typename LT, bool VEC>
 static cudaError_t launch_dbg_t(const Tables& t, const Inputs& in, const EstParams& p, const DebugOut& d, cudaStream_t st) {
-    auto kern = estimate_debug_kernel<LT>;
+    auto kern = estimate_debug_kernel<LT, VEC>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(WarpSmem));
     if (e != cudaSuccess) return e;
     kern<<<1, 32, sizeof(WarpSmem), st>>>(t, in, p, d);
@@ -356,8 +426,9 @@ cudaError_t launch_estimate_debug(const Tables& t, const Inputs& in, const EstPa
                                   uint8_t* filter_id, uint32_t* hist, unsigned long long* match, double* size_out,
                                   cudaStream_t st) {
     DebugOut d{v, k, row_costs, filter_id, hist, match, size_out};
-    if (in.label_dtype == ICR_LABELS_I64) return launch_dbg_t<int64_t>(t, in, p, d, st);
-    return launch_dbg_t<int32_t>(t, in, p, d, st);
+    const bool vec = vec_ok(t, in);
+    if (in.label_dtype == ICR_LABELS_I64) return vec ? launch_dbg_t<int64_t, true>(t, in, p, d, st) : launch_dbg_t<int64_t, false>(t, in, p, d, st);
+    return vec ? launch_dbg_t<int32_t, true>(t, in, p, d, st) : launch_dbg_t<int32_t, false>(t, in, p, d, st);
 }
 
 }  // namespace icr
