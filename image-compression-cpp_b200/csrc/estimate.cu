@@ -82,13 +82,6 @@ __device__ __forceinline__ int choose_geometry(int w, int h) {
     return lg;
 }
 
-// hist[C][b] += 1 unless b == 0: one predicated shared-memory reduction, no branch
-template <int C>
-__device__ __forceinline__ void hist_add(uint32_t hist_s, uint32_t b) {
-    asm volatile("{\n.reg .pred p;\nsetp.ne.u32 p, %1, 0;\n@p red.shared.add.u32 [%0+%2], 1;\n}"
-                 :: "r"(hist_s + 4u * b), "r"(b), "n"(C * 1024) : "memory");
-}
-
 // ---- stage rows yb .. yb+nr-1 of the bbox into the tile: lanes take the nr*w pixels in row-major order
 template <typename LT, bool FULL>
 __device__ __forceinline__ void stage_rows(const float* __restrict__ img, const LT* __restrict__ lab, int64_t HW, int W, LT key,
@@ -136,7 +129,7 @@ __device__ __forceinline__ void load_quad(const int64_t* p, int64_t (&l)[4]) {
 }
 
 template <typename LT, bool FULL>
-__device__ __forceinline__ void stage_rows_vec(const float* __restrict__ img, const LT* __restrict__ lab, int64_t HW, int W, LT key,
+__device__ __forceinline__ void stage_rows_vec(const float* __restrict__ img, const LT* __restrict__ lab, uint32_t HW, uint32_t base, int W, LT key,
                                                int w, int dx, int nq, float rnq, int nr, int s0, int R, int tst, uint32_t* tile, int lane) {
     const int total = nr * nq;
     constexpr int U = 2;                              // quads in flight per lane
@@ -152,11 +145,11 @@ __device__ __forceinline__ void stage_rows_vec(const float* __restrict__ img, co
             int slot = s0 + rr; if (slot > R) slot -= R + 1;
             xb[u] = q < total ? 4 * xq - dx : w;      // bbox column of the quad's first pixel; w = nothing to store
             dst[u] = slot * tst + 1 + xb[u];
-            const int off = rr * W + 4 * xq;
+            const uint32_t off = base + (uint32_t)(rr * W + 4 * xq);      // 32-bit offsets from the map's planes: one wide multiply-add per load
             if (q < total) {
                 r[u] = __ldg(reinterpret_cast<const float4*>(img + off));
-                g[u] = __ldg(reinterpret_cast<const float4*>(img + HW + off));
-                b[u] = __ldg(reinterpret_cast<const float4*>(img + 2 * HW + off));
+                g[u] = __ldg(reinterpret_cast<const float4*>(img + (off + HW)));
+                b[u] = __ldg(reinterpret_cast<const float4*>(img + (off + 2u * HW)));
                 if (!FULL) load_quad(lab + off, l[u]);
             }
         }
@@ -183,7 +176,6 @@ __device__ void warp_segment(const float* __restrict__ img, const LT* __restrict
     if (w <= 0 || h <= 0) { if (lane == 0) *out = 0.0; return; }   // src/compute_rewards.cu:164
     uint32_t* hist = sm.hist;
     uint32_t* tile = sm.tile;
-    const uint32_t hist_s = (uint32_t)__cvta_generic_to_shared(hist);
 
     const int lg = choose_geometry(w, h);
     const int S = 1 << lg, R = 32 >> lg;
@@ -210,10 +202,9 @@ __device__ void warp_segment(const float* __restrict__ img, const LT* __restrict
         __syncwarp();                                    // the previous group's walks are done with the slots about to be rewritten
         const int nr = min(R, h - yb);
         if (VEC) {
-            const float* ip = imgp + (int64_t)yb * W - dx;
-            const LT* lp = labp + (int64_t)yb * W - dx;
-            if (full) stage_rows_vec<LT, true>(ip, lp, HW, W, key, w, dx, nq, rnq, nr, s0, R, tst, tile, lane);
-            else stage_rows_vec<LT, false>(ip, lp, HW, W, key, w, dx, nq, rnq, nr, s0, R, tst, tile, lane);
+            const uint32_t base = (uint32_t)((bb.y + yb) * W + x0a);
+            if (full) stage_rows_vec<LT, true>(img, lab, (uint32_t)HW, base, W, key, w, dx, nq, rnq, nr, s0, R, tst, tile, lane);
+            else stage_rows_vec<LT, false>(img, lab, (uint32_t)HW, base, W, key, w, dx, nq, rnq, nr, s0, R, tst, tile, lane);
         } else {
             if (full) stage_rows<LT, true>(imgp + (int64_t)yb * W, labp + (int64_t)yb * W, HW, W, key, w, rw, nr, s0, R, tst, tile, lane);
             else stage_rows<LT, false>(imgp + (int64_t)yb * W, labp + (int64_t)yb * W, HW, W, key, w, rw, nr, s0, R, tst, tile, lane);
@@ -234,9 +225,11 @@ __device__ void warp_segment(const float* __restrict__ img, const LT* __restrict
         if (n > 0) {
             uint32_t left = trow[-1], ul = urow[-1];
             uint32_t l_lo = unpack_lo(left), l_hi = unpack_hi(left), ul_lo = unpack_lo(ul), ul_hi = unpack_hi(ul);
+            uint32_t cur = trow[0], up = urow[0];
 #pragma unroll 2
             for (int i = 0; i < n; ++i) {
-                const uint32_t cur = trow[i], up = urow[i];
+                // next pixel's loads first: they do not depend on this pixel's stores (one word past the strip is readable)
+                const uint32_t ncur = trow[i + 1], nup = urow[i + 1];
                 const uint32_t u_lo = unpack_lo(up), u_hi = unpack_hi(up);
                 const uint32_t pa = avg4(left, up);
                 const uint32_t pp = __byte_perm(paeth_h2(l_lo, u_lo, ul_lo), paeth_h2(l_hi, u_hi, ul_hi), 0x6420);
@@ -248,6 +241,7 @@ __device__ void warp_segment(const float* __restrict__ img, const LT* __restrict
                 par[i] = pa; ppr[i] = pp;
                 left = cur; l_lo = unpack_lo(cur); l_hi = unpack_hi(cur);
                 ul_lo = u_lo; ul_hi = u_hi;
+                cur = ncur; up = nup;
             }
         }
         for (int o = 1; o < S; o <<= 1) {
@@ -274,47 +268,49 @@ __device__ void warp_segment(const float* __restrict__ img, const LT* __restrict
             if (f == 2) { pred = urow; step = 1; }
             if (f == 3) { pred = par; step = 1; }
             if (f == 4) { pred = ppr; step = 1; }
+            uint32_t cur = trow[0], pr = *pred;
 #pragma unroll 2
             for (int i = 0; i < n; ++i) {
-                const uint32_t r = __vsub4(trow[i], *pred);
                 pred += step;
-                hist_add<0>(hist_s, __byte_perm(r, 0, 0x4440));
-                hist_add<1>(hist_s, __byte_perm(r, 0, 0x4441));
-                hist_add<2>(hist_s, __byte_perm(r, 0, 0x4442));
-                hist_add<3>(hist_s, r >> 24);
+                const uint32_t ncur = trow[i + 1], npr = *pred;      // loads of the next pixel ahead of this pixel's reductions
+                const uint32_t r = __vsub4(cur, pr);
+                atomicAdd(hist + __byte_perm(r, 0, 0x4440), 1u);
+                atomicAdd(hist + 256 + __byte_perm(r, 0, 0x4441), 1u);
+                atomicAdd(hist + 512 + __byte_perm(r, 0, 0x4442), 1u);
+                atomicAdd(hist + 768 + (r >> 24), 1u);
+                cur = ncur; pr = npr;
             }
         }
         s0 = s0 == 0 ? R : s0 - 1;                       // (yb + R + 1) mod (R+1)
     }
     __syncwarp();
 
-    // Rule H: H_c = -sum p log2 p = log2(n) - (sum c log2 c)/n ; lane owns 32 bins of channel lane/8
+    // Rule H: H_c = -sum p log2 p = log2(n) - (sum c log2 c)/n ; lane owns 32 bins of channel lane/8.
+    // Every pixel of the bbox was counted (bin 0 included), so the table is complete; it is left zeroed for the next segment.
     const uint32_t npx = (uint32_t)w * (uint32_t)h;
     double acc = 0.0;
-    uint32_t nz = 0;
     uint4* h4 = reinterpret_cast<uint4*>(hist) + lane * 8;
+    if (npx < (uint32_t)CLOG2_N) {               // no bin can lie beyond the c*log2(c) table: branch-free lookups (tab[0] = 0)
+#pragma unroll 2
+        for (int j = 0; j < 8; ++j) {
+            const uint4 q = h4[j];
+            h4[j] = make_uint4(0, 0, 0, 0);
+            if (DEBUG && dbg.hist) { uint32_t* d = dbg.hist + lane * 32 + j * 4; d[0] = q.x; d[1] = q.y; d[2] = q.z; d[3] = q.w; }
+            acc += (__ldg(clog2 + q.x) + __ldg(clog2 + q.y)) + (__ldg(clog2 + q.z) + __ldg(clog2 + q.w));
+        }
+    } else {
 #pragma unroll 1
-    for (int j = 0; j < 8; ++j) {
-        uint4 q = h4[j];
-        if (DEBUG && dbg.hist) {
-            uint32_t* d = dbg.hist + lane * 32 + j * 4;
-            d[0] = q.x; d[1] = q.y; d[2] = q.z; d[3] = q.w;
-        }
-        if (q.x | q.y | q.z | q.w) {
-            if (q.x) { acc += clog2_of(q.x, clog2); nz += q.x; }
-            if (q.y) { acc += clog2_of(q.y, clog2); nz += q.y; }
-            if (q.z) { acc += clog2_of(q.z, clog2); nz += q.z; }
-            if (q.w) { acc += clog2_of(q.w, clog2); nz += q.w; }
-            h4[j] = make_uint4(0, 0, 0, 0);      // leave the table clean for the next segment
+        for (int j = 0; j < 8; ++j) {
+            const uint4 q = h4[j];
+            h4[j] = make_uint4(0, 0, 0, 0);
+            if (DEBUG && dbg.hist) { uint32_t* d = dbg.hist + lane * 32 + j * 4; d[0] = q.x; d[1] = q.y; d[2] = q.z; d[3] = q.w; }
+            if (q.x) acc += clog2_of(q.x, clog2);
+            if (q.y) acc += clog2_of(q.y, clog2);
+            if (q.z) acc += clog2_of(q.z, clog2);
+            if (q.w) acc += clog2_of(q.w, clog2);
         }
     }
-    for (int o = 1; o < 8; o <<= 1) {
-        acc += __shfl_xor_sync(0xffffffffu, acc, o);
-        nz += __shfl_xor_sync(0xffffffffu, nz, o);
-    }
-    const uint32_t zeros = npx - nz;
-    if (zeros) acc += clog2_of(zeros, clog2);
-    if (DEBUG && dbg.hist) { __syncwarp(); if ((lane & 7) == 0) dbg.hist[(lane >> 3) * 256] = zeros; }
+    for (int o = 1; o < 8; o <<= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
     const double Hc = clog2_of(npx, clog2) / (double)npx - acc / (double)npx;       // log2(n) = (n log2 n)/n
     const double H0 = __shfl_sync(0xffffffffu, Hc, 0), H1 = __shfl_sync(0xffffffffu, Hc, 8);
     const double H2 = __shfl_sync(0xffffffffu, Hc, 16), H3 = __shfl_sync(0xffffffffu, Hc, 24);
