@@ -26,19 +26,12 @@ constexpr int EST_WARPS = 4;          // warps per CTA
 constexpr int MAXSW = 16;             // widest strip one lane walks
 constexpr int GRAB = 4;               // segments taken per global atomic
 
-// shared-memory budget per warp, maximised over the geometries choose_geometry() can return (w <= EST_MAX_W)
-constexpr int tile_words_max() {
-    int m = 0;
-    for (int lg = 0; lg <= 5; ++lg) {
-        int S = 1 << lg, R = 32 >> lg, w = MAXSW * S;
-        if (w > EST_MAX_W) w = EST_MAX_W;
-        int words = (R + 1) * (w + 2);
-        if (words > m) m = words;
-    }
-    return m;
-}
-constexpr int TILE_WORDS = tile_words_max() + 8;
-constexpr int PLANE_WORDS = 32 * MAXSW + 40;      // R rows x (w|1) words with w <= MAXSW * S
+// shared-memory budget per warp.  choose_geometry() only returns geometries whose (R+1) row slots of w+2 words fit TILE_CAP;
+// one row per group (S = 32) always fits: 2 * (EST_MAX_W + 2) <= TILE_CAP.
+constexpr int TILE_CAP = 576;
+constexpr int TILE_WORDS = TILE_CAP + 8;
+constexpr int PLANE_WORDS = TILE_CAP;             // R rows x (w|1) words < (R+1) * (w+2)
+static_assert(2 * (EST_MAX_W + 2) <= TILE_CAP, "a single-row group of the widest bbox must fit the tile");
 
 struct __align__(16) WarpSmem {
     uint32_t hist[1024];              // 4 x 256 residual histogram
@@ -77,7 +70,7 @@ __device__ __forceinline__ int choose_geometry(int w, int h) {
         const int sw = (w + (1 << l) - 1) >> l;
         const int groups = ((h << l) + 31) >> 5;
         const int cost = groups * (20 * sw + 14 + 3 * l);      // per group: sw pixel steps (~70 instructions each) + set-up, butterfly, choice
-        if (sw <= MAXSW && cost < best) { best = cost; lg = l; }
+        if (sw <= MAXSW && ((32 >> l) + 1) * (w + 2) <= TILE_CAP && cost < best) { best = cost; lg = l; }
     }
     return lg;
 }
