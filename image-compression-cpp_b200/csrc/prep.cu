@@ -4,10 +4,12 @@
 // Rule L is a circular presence bitmap in shared memory indexed by (label mod capacity): while the
 // spread max-min is below the capacity the residues are distinct, so sweep 1 sets bits and finds
 // min/max at once; a popcount prefix scan then gives rank = number of set bits walking up from the
-// minimum's slot.  No sort, no host sync on K.  Sweep 2 turns labels into ranks and accumulates
-// Rule S, warp-aggregated: runs of equal ids along x collapse to one update of a shared-memory
-// table, and bbox atomics are skipped when they cannot change the value.  The image is not touched
-// here: the estimator masks by comparing raw labels with the segment's key (its original label).
+// minimum's slot.  No sort, no host sync on K.
+// Sweep 2 works on RUNS, not pixels: a warp looks at 32*VEC consecutive pixels, marks the pixels where
+// the label changes (or a row / the warp's span starts), and only those run heads rank their label
+// and update the shared-memory stats table: one add for the count and four min/max for the bbox per
+// run, all unconditional shared-memory atomics issued for every head of the span at once.  The image
+// is not touched here: the estimator masks by comparing raw labels with the segment's key.
 // The last CTA to finish also scans the per-map segment counts into the flat work list the
 // estimator's dynamic scheduler walks.
 #include "icr_internal.h"
@@ -18,7 +20,7 @@ namespace icr {
 constexpr int PREP_T = 512;
 
 template <typename LT, int VEC>
-__device__ __forceinline__ void load_labels(const LT* lab, int64_t p, bool inrange, long long (&out)[VEC]) {
+__device__ __forceinline__ void load_labels(const LT* lab, int64_t p, bool inrange, LT (&out)[VEC]) {
     if constexpr (VEC == 4 && sizeof(LT) == 4) {
         int4 q = inrange ? __ldg(reinterpret_cast<const int4*>(lab + p)) : make_int4(0, 0, 0, 0);
         out[0] = q.x; out[1] = q.y; out[2] = q.z; out[3] = q.w;
@@ -27,12 +29,84 @@ __device__ __forceinline__ void load_labels(const LT* lab, int64_t p, bool inran
         if (inrange) { a = __ldg(reinterpret_cast<const longlong2*>(lab + p)); b = __ldg(reinterpret_cast<const longlong2*>(lab + p + 2)); }
         out[0] = a.x; out[1] = a.y; out[2] = b.x; out[3] = b.y;
     } else {
-        out[0] = inrange ? (long long)lab[p] : 0;
+        out[0] = inrange ? __ldg(lab + p) : (LT)0;
+    }
+}
+
+// shared-memory stats table of one map (or its rows in global memory when K > KS_SMEM): struct of arrays, element stride bst
+struct StatsPtr { int32_t *cnt, *bx0, *by0, *bx1, *by1; int bst; };
+
+// ---- sweep 2 on runs.  SMEM selects shared-memory atomics at compile time (a generic pointer would cost an address-space
+// check per atomic).
+template <typename LT, int VEC, bool SMEM, bool COMPACT_OUT, class RankOf>
+__device__ __forceinline__ void sweep_runs(const LT* __restrict__ lab, int64_t HW, int W, const StatsPtr& st, RankOf rank_of,
+                                           int32_t* __restrict__ compact_row) {
+    const int tid = threadIdx.x, lane = tid & 31;
+    // position of this thread's first pixel; advanced incrementally (W % VEC == 0 on the vector path keeps a group in one row)
+    int64_t p = (int64_t)tid * VEC;
+    int y = (int)(p / W), x = (int)(p - (int64_t)y * W);
+    const int stepx = (PREP_T * VEC) % W, stepy = (PREP_T * VEC) / W;
+    for (int64_t base = 0; base < HW; base += (int64_t)PREP_T * VEC, p += (int64_t)PREP_T * VEC) {
+        const bool in = p < HW;
+        LT l[VEC];
+        load_labels<LT, VEC>(lab, p, in, l);
+        if (COMPACT_OUT && in) {
+            uint32_t id[VEC];
+#pragma unroll
+            for (int i = 0; i < VEC; ++i) id[i] = (i > 0 && l[i] == l[i - 1]) ? id[i - 1] : rank_of(l[i]);
+            int32_t* co = compact_row + p;
+            if constexpr (VEC == 4) *reinterpret_cast<int4*>(co) = make_int4((int)id[0], (int)id[1], (int)id[2], (int)id[3]);
+            else co[0] = (int)id[0];
+        }
+        // ---- run heads among this lane's pixels: the label differs from the pixel before, or a row / the warp's span starts
+        const LT prevl = __shfl_up_sync(0xffffffffu, l[VEC - 1], 1);
+        uint32_t hm = 0;
+        if (in) {
+            if (lane == 0 || x == 0 || l[0] != prevl) hm = 1u;
+#pragma unroll
+            for (int i = 1; i < VEC; ++i) if (l[i] != l[i - 1]) hm |= 1u << i;
+        }
+        // where the next head after this lane's pixels stands, in pixels from the span's start (the span's end if none)
+        const uint32_t has = __ballot_sync(0xffffffffu, hm != 0u);
+        const uint32_t inm = __ballot_sync(0xffffffffu, in);
+        const uint32_t above = lane == 31 ? 0u : (has & (0xffffffffu << (lane + 1)));
+        const int nl = above ? __ffs(above) - 1 : 32;                         // next lane holding a head
+        const int first = __ffs(hm) - 1;                                        // -1 if none
+        const int nfirst = __shfl_sync(0xffffffffu, first, nl & 31);
+        const int next_after = above ? nl * VEC + nfirst : __popc(inm) * VEC;
+        // ---- every lane takes its lowest unprocessed head; usually one round
+        while (__any_sync(0xffffffffu, hm != 0u)) {
+            if (hm) {
+                const int i = __ffs(hm) - 1;
+                hm &= hm - 1;
+                LT lv = l[0];
+#pragma unroll
+                for (int j = 1; j < VEC; ++j) if (i == j) lv = l[j];
+                const int endpos = hm ? lane * VEC + (__ffs(hm) - 1) : next_after;
+                const int n = endpos - (lane * VEC + i);
+                const int kc = (int)rank_of(lv), k = kc * st.bst;
+                const int xa = x + i;
+                if (SMEM) {
+                    atomicAdd(st.cnt + kc, n);
+                    atomicMin(st.bx0 + k, xa); atomicMax(st.bx1 + k, xa + n - 1);
+                    atomicMin(st.by0 + k, y); atomicMax(st.by1 + k, y);
+                } else {
+                    // table rows in global memory (more than KS_SMEM segments): skip the atomics that cannot change anything
+                    atomicAdd(st.cnt + kc, n);
+                    if (xa < st.bx0[k]) atomicMin(st.bx0 + k, xa);
+                    if (xa + n - 1 > st.bx1[k]) atomicMax(st.bx1 + k, xa + n - 1);
+                    if (y < st.by0[k]) atomicMin(st.by0 + k, y);
+                    if (y > st.by1[k]) atomicMax(st.by1 + k, y);
+                }
+            }
+        }
+        x += stepx; y += stepy;
+        if (x >= W) { x -= W; ++y; }
     }
 }
 
 template <typename LT, int VEC, bool COMPACT_OUT>
-__global__ void __launch_bounds__(PREP_T) prep_kernel(const LT* __restrict__ labels, Tables t, int cap_words,
+__global__ void __launch_bounds__(PREP_T, 2) prep_kernel(const LT* __restrict__ labels, Tables t, int cap_words,
                                                        int32_t* __restrict__ compact_out) {
     extern __shared__ uint32_t smem[];
     uint32_t* bitmap = smem;
@@ -55,33 +129,34 @@ __global__ void __launch_bounds__(PREP_T) prep_kernel(const LT* __restrict__ lab
     __syncthreads();
 
     // ---- sweep 1: min / max and the circular presence bitmap (plain read first: almost every bit is already set)
-    long long lo = LLONG_MAX, hi = LLONG_MIN;
+    LT lo = sizeof(LT) == 8 ? (LT)LLONG_MAX : (LT)INT_MAX, hi = sizeof(LT) == 8 ? (LT)LLONG_MIN : (LT)INT_MIN;
     for (int64_t base = 0; base < HW; base += (int64_t)PREP_T * VEC) {
-        int64_t p = base + (int64_t)tid * VEC;
-        long long l[VEC];
-        bool in = p < HW;
+        const int64_t p = base + (int64_t)tid * VEC;
+        LT l[VEC];
+        const bool in = p < HW;
         load_labels<LT, VEC>(lab, p, in, l);
         if (in) {
 #pragma unroll
             for (int i = 0; i < VEC; ++i) {
                 if (i > 0 && l[i] == l[i - 1]) continue;
                 lo = min(lo, l[i]); hi = max(hi, l[i]);
-                uint32_t idx = (uint32_t)l[i] & cmask, bit = 1u << (idx & 31);
+                const uint32_t idx = (uint32_t)l[i] & cmask, bit = 1u << (idx & 31);
                 if (!(bitmap[idx >> 5] & bit)) atomicOr(&bitmap[idx >> 5], bit);
             }
         }
     }
+    long long lo64 = lo, hi64 = hi;
     for (int o = 16; o; o >>= 1) {
-        lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, o));
-        hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+        lo64 = min(lo64, __shfl_xor_sync(0xffffffffu, lo64, o));
+        hi64 = max(hi64, __shfl_xor_sync(0xffffffffu, hi64, o));
     }
-    if (lane == 0) { red_lo[wid] = lo; red_hi[wid] = hi; }
+    if (lane == 0) { red_lo[wid] = lo64; red_hi[wid] = hi64; }
     __syncthreads();
     if (tid == 0) {
-        for (int i = 1; i < PREP_T / 32; ++i) { lo = min(lo, red_lo[i]); hi = max(hi, red_hi[i]); }
-        s_min = lo;
+        for (int i = 1; i < PREP_T / 32; ++i) { lo64 = min(lo64, red_lo[i]); hi64 = max(hi64, red_hi[i]); }
+        s_min = lo64;
         // the spread must fit the bitmap (unsigned arithmetic also covers overflow of hi-lo)
-        s_bad = ((unsigned long long)hi - (unsigned long long)lo > (unsigned long long)cmask) ? ST_LABEL_RANGE : ST_OK;
+        s_bad = ((unsigned long long)hi64 - (unsigned long long)lo64 > (unsigned long long)cmask) ? ST_LABEL_RANGE : ST_OK;
     }
     __syncthreads();
     const long long lmin = s_min;
@@ -109,10 +184,11 @@ __global__ void __launch_bounds__(PREP_T) prep_kernel(const LT* __restrict__ lab
 
     if (!bad) {
         const uint32_t pmin = prefix[smin >> 5] + __popc(bitmap[smin >> 5] & ((1u << (smin & 31)) - 1u));
-        auto rank_of = [&](uint32_t slot) -> uint32_t {
+        auto rank_slot = [&](uint32_t slot) -> uint32_t {
             uint32_t ps = prefix[slot >> 5] + __popc(bitmap[slot >> 5] & ((1u << (slot & 31)) - 1u));
             return slot >= smin ? ps - pmin : (uint32_t)K - (pmin - ps);
         };
+        auto rank_of = [&](LT label) -> uint32_t { return rank_slot((uint32_t)label & cmask); };
         // ---- keys: original label of each compact id, ascending
         long long* keys = t.keys + (int64_t)v * t.Kmax;
         for (int w = tid; w < cap_words; w += PREP_T) {
@@ -121,75 +197,28 @@ __global__ void __launch_bounds__(PREP_T) prep_kernel(const LT* __restrict__ lab
                 int b = __ffs(bits) - 1;
                 bits &= bits - 1;
                 uint32_t slot = (uint32_t)w * 32u + b;
-                keys[rank_of(slot)] = lmin + (long long)((slot - smin) & cmask);
+                keys[rank_slot(slot)] = lmin + (long long)((slot - smin) & cmask);
             }
         }
         // ---- stats tables: shared memory when K fits, else straight into the global rows
         int32_t* g_cnt = t.counts + (int64_t)v * t.Kmax;
         int32_t* g_bb = reinterpret_cast<int32_t*>(t.bboxes + (int64_t)v * t.Kmax);
-        const bool in_smem = K <= KS_SMEM;
-        int32_t *cnt, *bx0, *by0, *bx1, *by1;
-        if (in_smem) { cnt = stab; bx0 = stab + KS_SMEM; by0 = stab + 2 * KS_SMEM; bx1 = stab + 3 * KS_SMEM; by1 = stab + 4 * KS_SMEM; }
-        else { cnt = g_cnt; bx0 = g_bb; by0 = g_bb + 1; bx1 = g_bb + 2; by1 = g_bb + 3; }
-        const int bst = in_smem ? 1 : 4;    // bbox element stride
-        for (int k = tid; k < K; k += PREP_T) { cnt[k] = 0; bx0[k * bst] = W; by0[k * bst] = H; bx1[k * bst] = -1; by1[k * bst] = -1; }
-        __syncthreads();
-
-        // ---- sweep 2: ranks and stats.  A lane whose VEC pixels share one id is a unit; consecutive units with the
-        // same id on the same row form a run, updated once by its head lane.
-        for (int64_t base = 0; base < HW; base += (int64_t)PREP_T * VEC) {
-            int64_t p = base + (int64_t)tid * VEC;
-            const bool in = p < HW;
-            long long l[VEC];
-            load_labels<LT, VEC>(lab, p, in, l);
-            uint32_t id[VEC];
-#pragma unroll
-            for (int i = 0; i < VEC; ++i) {
-                if (i > 0 && l[i] == l[i - 1]) { id[i] = id[i - 1]; continue; }
-                id[i] = in ? rank_of((uint32_t)l[i] & cmask) : 0u;
-            }
-            if (COMPACT_OUT && in) {
-                int32_t* co = compact_out + (int64_t)v * HW + p;
-                if constexpr (VEC == 4) *reinterpret_cast<int4*>(co) = make_int4((int)id[0], (int)id[1], (int)id[2], (int)id[3]);
-                else co[0] = (int)id[0];
-            }
-            const int y = (int)(p / W), x = (int)(p - (int64_t)y * W);
-            bool uni = in;
-#pragma unroll
-            for (int i = 1; i < VEC; ++i) uni = uni && id[i] == id[0];
-            const uint32_t pid = __shfl_up_sync(0xffffffffu, id[0], 1);
-            const int py = __shfl_up_sync(0xffffffffu, y, 1);
-            const bool puni = __shfl_up_sync(0xffffffffu, uni, 1);
-            const bool joins = lane > 0 && uni && puni && pid == id[0] && py == y;
-            const uint32_t breaks = __ballot_sync(0xffffffffu, !joins);
-            if (uni && !joins) {
-                uint32_t above = lane == 31 ? 0u : (breaks & (0xffffffffu << (lane + 1)));
-                int next = above ? __ffs(above) - 1 : 32;
-                int n = (next - lane) * VEC;
-                int k = (int)id[0];
-                atomicAdd(&cnt[k], n);
-                if (x < bx0[k * bst]) atomicMin(&bx0[k * bst], x);
-                if (y < by0[k * bst]) atomicMin(&by0[k * bst], y);
-                if (x + n - 1 > bx1[k * bst]) atomicMax(&bx1[k * bst], x + n - 1);
-                if (y > by1[k * bst]) atomicMax(&by1[k * bst], y);
-            } else if (in && !uni) {
-#pragma unroll
-                for (int i = 0; i < VEC; ++i) {
-                    int k = (int)id[i];
-                    atomicAdd(&cnt[k], 1);
-                    if (x + i < bx0[k * bst]) atomicMin(&bx0[k * bst], x + i);
-                    if (y < by0[k * bst]) atomicMin(&by0[k * bst], y);
-                    if (x + i > bx1[k * bst]) atomicMax(&bx1[k * bst], x + i);
-                    if (y > by1[k * bst]) atomicMax(&by1[k * bst], y);
-                }
-            }
-        }
-        if (in_smem) {
+        int32_t* compact_row = COMPACT_OUT ? compact_out + (int64_t)v * HW : nullptr;
+        if (K <= KS_SMEM) {
+            const StatsPtr st{stab, stab + KS_SMEM, stab + 2 * KS_SMEM, stab + 3 * KS_SMEM, stab + 4 * KS_SMEM, 1};
+            for (int k = tid; k < K; k += PREP_T) { st.cnt[k] = 0; st.bx0[k] = W; st.by0[k] = H; st.bx1[k] = -1; st.by1[k] = -1; }
+            __syncthreads();
+            sweep_runs<LT, VEC, true, COMPACT_OUT>(lab, HW, W, st, rank_of, compact_row);
             __syncthreads();
             for (int k = tid; k < K; k += PREP_T) {
-                g_cnt[k] = cnt[k];
-                t.bboxes[(int64_t)v * t.Kmax + k] = make_int4(bx0[k], by0[k], bx1[k], by1[k]);
+                g_cnt[k] = st.cnt[k];
+                t.bboxes[(int64_t)v * t.Kmax + k] = make_int4(st.bx0[k], st.by0[k], st.bx1[k], st.by1[k]);
             }
+        } else {
+            const StatsPtr st{g_cnt, g_bb, g_bb + 1, g_bb + 2, g_bb + 3, 4};
+            for (int k = tid; k < K; k += PREP_T) { g_cnt[k] = 0; g_bb[4 * k] = W; g_bb[4 * k + 1] = H; g_bb[4 * k + 2] = -1; g_bb[4 * k + 3] = -1; }
+            __syncthreads();
+            sweep_runs<LT, VEC, false, COMPACT_OUT>(lab, HW, W, st, rank_of, compact_row);
         }
     }
 
