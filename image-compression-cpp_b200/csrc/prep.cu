@@ -46,10 +46,15 @@ __device__ __forceinline__ void sweep_runs(const LT* __restrict__ lab, int64_t H
     int64_t p = (int64_t)tid * VEC;
     int y = (int)(p / W), x = (int)(p - (int64_t)y * W);
     const int stepx = (PREP_T * VEC) % W, stepy = (PREP_T * VEC) / W;
+    LT nxt[VEC];
+    load_labels<LT, VEC>(lab, p, p < HW, nxt);
     for (int64_t base = 0; base < HW; base += (int64_t)PREP_T * VEC, p += (int64_t)PREP_T * VEC) {
         const bool in = p < HW;
         LT l[VEC];
-        load_labels<LT, VEC>(lab, p, in, l);
+#pragma unroll
+        for (int i = 0; i < VEC; ++i) l[i] = nxt[i];
+        // the next step's labels are requested before this step's work: one memory latency per sweep, not per step
+        load_labels<LT, VEC>(lab, p + (int64_t)PREP_T * VEC, p + (int64_t)PREP_T * VEC < HW, nxt);
         if (COMPACT_OUT && in) {
             uint32_t id[VEC];
 #pragma unroll
@@ -130,11 +135,15 @@ __global__ void __launch_bounds__(PREP_T, 2) prep_kernel(const LT* __restrict__ 
 
     // ---- sweep 1: min / max and the circular presence bitmap (plain read first: almost every bit is already set)
     LT lo = sizeof(LT) == 8 ? (LT)LLONG_MAX : (LT)INT_MAX, hi = sizeof(LT) == 8 ? (LT)LLONG_MIN : (LT)INT_MIN;
+    LT nxt[VEC];
+    load_labels<LT, VEC>(lab, (int64_t)tid * VEC, (int64_t)tid * VEC < HW, nxt);
     for (int64_t base = 0; base < HW; base += (int64_t)PREP_T * VEC) {
         const int64_t p = base + (int64_t)tid * VEC;
         LT l[VEC];
         const bool in = p < HW;
-        load_labels<LT, VEC>(lab, p, in, l);
+#pragma unroll
+        for (int i = 0; i < VEC; ++i) l[i] = nxt[i];
+        load_labels<LT, VEC>(lab, p + (int64_t)PREP_T * VEC, p + (int64_t)PREP_T * VEC < HW, nxt);
         if (in) {
 #pragma unroll
             for (int i = 0; i < VEC; ++i) {
