@@ -302,6 +302,12 @@ def main():
     achieved = float(alg_bytes / (kavg[top] * 1e-3) / 1e9)
     path_gbs = float(alg_bytes / (ms / args.steps * 1e-3) / 1e9)
 
+    traffic = None
+    try:                          # dram bytes per launch of the same kernel from the committed ncu --set full capture
+        with open(os.path.join(ROOT, "profiles", "r01_traffic.json")) as f:
+            traffic = json.load(f).get(names[top])
+    except Exception:
+        pass
     line = {
         "metric": METRIC, "value": value, "unit": "images/sec", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
@@ -314,7 +320,8 @@ def main():
                 "api": "icr_compute_rewards_host (C ABI, pinned host buffers)"},
         "gpu_launches": launches,
         "roofline": {"bound": "hbm", "kernel": names[top], "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": float(alg_bytes),
+                     "traffic": traffic, "traffic_source": "profiles/r01_traffic.json (ncu --set full, per launch)" if traffic else None,
+                     "peak_source": peak_src, "algorithmic_bytes_per_launch": float(alg_bytes),
                      "kernel_ms": {n: float(k) for n, k in zip(names, kavg)}, "whole_path_gbs": path_gbs, "whole_path_frac": path_gbs / peak},
         "clocks": clk.summary(),
     }
