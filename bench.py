@@ -25,7 +25,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-PER_GPU = 512
+PER_GPU = int(os.environ.get("ICR_BENCH_PER_GPU", "512"))      # images per GPU and step (override only for experiments)
 POOL = 64           # distinct synthetic images per rank; the shard tiles them (addresses differ, so no cache reuse)
 H = W = 224
 METRIC = "images/sec (slice+PNG-size reward)"

@@ -24,7 +24,6 @@ namespace icr {
 
 constexpr int EST_WARPS = 4;          // warps per CTA
 constexpr int MAXSW = 16;             // widest strip one lane walks
-constexpr int GRAB = 4;               // segments taken per global atomic
 
 // shared-memory budget per warp.  choose_geometry() only returns geometries whose (R+1) row slots of w+2 words fit TILE_CAP;
 // one row per group (S = 32) always fits: 2 * (EST_MAX_W + 2) <= TILE_CAP.
@@ -73,6 +72,21 @@ __device__ __forceinline__ int choose_geometry(int w, int h) {
         if (sw <= MAXSW && ((32 >> l) + 1) * (w + 2) <= TILE_CAP && cost < best) { best = cost; lg = l; }
     }
     return lg;
+}
+
+// The map v with seg_prefix[v] <= flat < seg_prefix[v+1], searched by the whole warp: 32 probes per round, so two
+// dependent loads for up to 1024 maps instead of a lane's ten-step binary search.
+__device__ __forceinline__ int locate_map(const int32_t* __restrict__ sp, int V, int flat, int lane) {
+    int lo = 0, n = V;                                  // answer in [lo, lo+n); sp[lo] <= flat
+    while (n > 1) {
+        const int step = (n + 31) >> 5;
+        const int idx = lo + (lane + 1) * step;
+        const bool le = idx < lo + n && __ldg(sp + idx) <= flat;      // monotone in lane
+        const int c = __popc(__ballot_sync(0xffffffffu, le));
+        lo += c * step;
+        n = min(step, n - c * step);
+    }
+    return lo;
 }
 
 // ---- stage rows yb .. yb+nr-1 of the bbox into the tile: lanes take the nr*w pixels in row-major order
@@ -330,28 +344,23 @@ __global__ void __launch_bounds__(EST_WARPS * 32) estimate_kernel(Tables t, Inpu
     const int total = t.seg_prefix[t.V];
     const LT* labels = static_cast<const LT*>(in.labels);
     DebugOut none{};
-    for (;;) {
-        int base = lane == 0 ? atomicAdd(&t.sched[1], GRAB) : 0;
-        base = __shfl_sync(0xffffffffu, base, 0);
-        if (base >= total) break;
-        // lanes 0..GRAB-1 locate their flat index: the map v with seg_prefix[v] <= flat < seg_prefix[v+1]
-        int mv = 0, mk = 0;
-        if (lane < GRAB && base + lane < total) {
-            const int flat = base + lane;
-            int lo = 0, hi = t.V;                       // invariant: seg_prefix[lo] <= flat < seg_prefix[hi]
-            while (hi - lo > 1) { int mid = (lo + hi) >> 1; if (__ldg(t.seg_prefix + mid) <= flat) lo = mid; else hi = mid; }
-            mv = lo; mk = flat - __ldg(t.seg_prefix + lo);
-        }
-        const int cnt = min(GRAB, total - base);
-        for (int j = 0; j < cnt; ++j) {
-            const int v = __shfl_sync(0xffffffffu, mv, j), k = __shfl_sync(0xffffffffu, mk, j);
-            const int4 bb = __ldg(t.bboxes + (int64_t)v * t.Kmax + k);
-            if (for_big_kernel(bb.z - bb.x + 1, bb.w - bb.y + 1, p.L_min)) continue;
-            const LT key = (LT)__ldg(t.keys + (int64_t)v * t.Kmax + k);
-            warp_segment<LT, false, VEC>(in.images + (int64_t)(v / in.S) * 3 * HW, labels + (int64_t)v * HW, HW, t.W, key,
-                                    __ldg(t.counts + (int64_t)v * t.Kmax + k), bb, sm, p, t.clog2,
-                                    t.seg_sizes + (int64_t)v * t.Kmax + k, none);
-        }
+    // One segment per request: a warp's share of the SM makes a segment take ~15 us, so handing out several at a time left
+    // warps idle for tens of microseconds at the end of the launch.  The request for the next segment is issued before
+    // the current one is worked on, so its latency is hidden.
+    int flat = lane == 0 ? atomicAdd(&t.sched[1], 1) : 0;
+    flat = __shfl_sync(0xffffffffu, flat, 0);
+    while (flat < total) {
+        const int fut = lane == 0 ? atomicAdd(&t.sched[1], 1) : 0;
+        const int v = locate_map(t.seg_prefix, t.V, flat, lane);
+        const int k = flat - __ldg(t.seg_prefix + v);
+        const int64_t row = (int64_t)v * t.Kmax + k;
+        const int4 bb = __ldg(t.bboxes + row);
+        const LT key = (LT)__ldg(t.keys + row);
+        const int count = __ldg(t.counts + row);
+        if (!for_big_kernel(bb.z - bb.x + 1, bb.w - bb.y + 1, p.L_min))
+            warp_segment<LT, false, VEC>(in.images + (int64_t)(v / in.S) * 3 * HW, labels + (int64_t)v * HW, HW, t.W, key, count, bb, sm, p,
+                                         t.clog2, t.seg_sizes + row, none);
+        flat = __shfl_sync(0xffffffffu, fut, 0);
     }
 }
 
