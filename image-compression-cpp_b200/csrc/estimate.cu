@@ -318,12 +318,13 @@ __device__ void warp_segment(const float* __restrict__ img, const LT* __restrict
         }
     }
     for (int o = 1; o < 8; o <<= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-    const double Hc = clog2_of(npx, clog2) / (double)npx - acc / (double)npx;       // log2(n) = (n log2 n)/n
+    const double Hc = (clog2_of(npx, clog2) - acc) / (double)npx;                    // log2(n) = (n log2 n)/n
     const double H0 = __shfl_sync(0xffffffffu, Hc, 0), H1 = __shfl_sync(0xffffffffu, Hc, 8);
     const double H2 = __shfl_sync(0xffffffffu, Hc, 16), H3 = __shfl_sync(0xffffffffu, Hc, 24);
     if (lane == 0) {
         const double Hbar = ((H0 + H2) + (H1 + H3)) / 4.0;     // tree of mean_channels_kernel (:314-328)
-        const double sz = size_formula(Hbar, 0, 0, 0, 4ull * npx, h, p);
+        // Rule Z with no matches (f = 0): (1-0)*b_lit + 0*b_match is b_lit exactly, so the match term's division is not evaluated
+        const double sz = (p.overhead + (double)h) + ((double)(4ull * npx) * (Hbar + p.beta)) / 8.0;
         *out = sz;
         if (DEBUG) {
             if (dbg.match) { dbg.match[0] = 0; dbg.match[1] = 0; dbg.match[2] = 0; }
