@@ -23,6 +23,8 @@ struct Tables {            // device pointers into the workspace, V label maps
     int32_t* seg_prefix;   // [V+1] exclusive scan of the segment counts of the maps with status OK
     int32_t* sched;        // [4] {prep CTAs done, estimate work cursor, -, -}
     uint8_t* big_filter;   // [V*BIG_CTAS, H] filter ids of the segment a big-kernel CTA is working on
+    uint2* runs;           // [V, run_cap] label runs of a map found by prep's first sweep {slot | (len-1)<<20, y<<16 | x}
+    int run_cap;           // 0 = no run list (very wide maps)
     const double* clog2;   // [CLOG2_N] c*log2(c)
     int V, H, W, Kmax;
 };
@@ -58,6 +60,13 @@ inline int64_t label_capacity(int H, int W) {
     int64_t cap = 65536;
     while (cap < hw) cap <<= 1;
     return cap;
+}
+
+// run-list capacity per map: an average run of 8 pixels or more fits; beyond it prep falls back to a second pixel sweep
+inline int run_capacity(int H, int W) {
+    if (W > 4096 || H > 65535) return 0;          // record packing: 12 bits of length, 16 bits of x and y
+    int64_t c = (int64_t)H * W / 8;
+    return (int)(c < 1024 ? 1024 : c);
 }
 
 // launchers (each returns the cudaError_t of its launches)

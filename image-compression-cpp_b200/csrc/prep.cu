@@ -110,6 +110,83 @@ __device__ __forceinline__ void sweep_runs(const LT* __restrict__ lab, int64_t H
     }
 }
 
+// ---- sweep 1 on runs: the same head detection as sweep_runs; a head marks its label in the presence bitmap, feeds min/max and
+// appends one record {slot | (len-1) << 20, y << 16 | x} to the map's run list (one shared-memory atomic per warp and round).
+// With the list complete, Rule S needs no second pass over the pixels: sweep_list walks the records.
+template <typename LT, int VEC>
+__device__ __forceinline__ void sweep_mark(const LT* __restrict__ lab, int64_t HW, int W, uint32_t* bitmap, uint32_t cmask, LT& lo, LT& hi,
+                                           uint2* __restrict__ runs, int run_cap, int* s_nruns) {
+    const int tid = threadIdx.x, lane = tid & 31;
+    int64_t p = (int64_t)tid * VEC;
+    int y = (int)(p / W), x = (int)(p - (int64_t)y * W);
+    const int stepx = (PREP_T * VEC) % W, stepy = (PREP_T * VEC) / W;
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    LT nxt[VEC];
+    load_labels<LT, VEC>(lab, p, p < HW, nxt);
+    for (int64_t base = 0; base < HW; base += (int64_t)PREP_T * VEC, p += (int64_t)PREP_T * VEC) {
+        const bool in = p < HW;
+        LT l[VEC];
+#pragma unroll
+        for (int i = 0; i < VEC; ++i) l[i] = nxt[i];
+        load_labels<LT, VEC>(lab, p + (int64_t)PREP_T * VEC, p + (int64_t)PREP_T * VEC < HW, nxt);
+        const LT prevl = __shfl_up_sync(0xffffffffu, l[VEC - 1], 1);
+        uint32_t hm = 0;
+        if (in) {
+            if (lane == 0 || x == 0 || l[0] != prevl) hm = 1u;
+#pragma unroll
+            for (int i = 1; i < VEC; ++i) if (l[i] != l[i - 1]) hm |= 1u << i;
+        }
+        const uint32_t has = __ballot_sync(0xffffffffu, hm != 0u);
+        const uint32_t inm = __ballot_sync(0xffffffffu, in);
+        const uint32_t above = lane == 31 ? 0u : (has & (0xffffffffu << (lane + 1)));
+        const int nl = above ? __ffs(above) - 1 : 32;
+        const int first = __ffs(hm) - 1;
+        const int nfirst = __shfl_sync(0xffffffffu, first, nl & 31);
+        const int next_after = above ? nl * VEC + nfirst : __popc(inm) * VEC;
+        uint32_t act;
+        while ((act = __ballot_sync(0xffffffffu, hm != 0u)) != 0u) {
+            int rbase = 0;
+            if (lane == 0) rbase = atomicAdd(s_nruns, __popc(act));
+            rbase = __shfl_sync(0xffffffffu, rbase, 0);
+            if (hm) {
+                const int i = __ffs(hm) - 1;
+                hm &= hm - 1;
+                LT lv = l[0];
+#pragma unroll
+                for (int j = 1; j < VEC; ++j) if (i == j) lv = l[j];
+                const int endpos = hm ? lane * VEC + (__ffs(hm) - 1) : next_after;
+                const int n = endpos - (lane * VEC + i);
+                lo = min(lo, lv); hi = max(hi, lv);
+                const uint32_t idx = (uint32_t)lv & cmask, bit = 1u << (idx & 31);
+                if (!(bitmap[idx >> 5] & bit)) atomicOr(&bitmap[idx >> 5], bit);
+                const int pos = rbase + __popc(act & lt_mask);
+                if (pos < run_cap) runs[pos] = make_uint2(idx | (uint32_t)(n - 1) << 20, (uint32_t)y << 16 | (uint32_t)(x + i));
+            }
+        }
+        x += stepx; y += stepy;
+        if (x >= W) { x -= W; ++y; }
+    }
+}
+
+template <bool SMEM, class RankSlot>
+__device__ __forceinline__ void sweep_list(const uint2* runs, int nruns, const StatsPtr& st, RankSlot rank_slot) {
+    for (int r = threadIdx.x; r < nruns; r += PREP_T) {
+        const uint2 rec = runs[r];                    // written by this CTA before a barrier: a plain (coherent) load
+        const int n = (int)(rec.x >> 20) + 1, y = (int)(rec.y >> 16), xa = (int)(rec.y & 0xffffu);
+        const int kc = (int)rank_slot(rec.x & 0xfffffu), k = kc * st.bst;
+        atomicAdd(st.cnt + kc, n);
+        if (SMEM) {
+            atomicMin(st.bx0 + k, xa); atomicMax(st.bx1 + k, xa + n - 1);
+            atomicMin(st.by0 + k, y); atomicMax(st.by1 + k, y);
+        } else {
+            if (xa < st.bx0[k]) atomicMin(st.bx0 + k, xa);
+            if (xa + n - 1 > st.bx1[k]) atomicMax(st.bx1 + k, xa + n - 1);
+            if (y < st.by0[k]) atomicMin(st.by0 + k, y);
+            if (y > st.by1[k]) atomicMax(st.by1 + k, y);
+        }
+    }
+}
+
 template <typename LT, int VEC, bool COMPACT_OUT>
 __global__ void __launch_bounds__(PREP_T, 2) prep_kernel(const LT* __restrict__ labels, Tables t, int cap_words,
                                                        int32_t* __restrict__ compact_out) {
@@ -120,7 +197,7 @@ __global__ void __launch_bounds__(PREP_T, 2) prep_kernel(const LT* __restrict__ 
     __shared__ long long red_lo[PREP_T / 32], red_hi[PREP_T / 32];
     __shared__ uint32_t warp_tot[PREP_T / 32];
     __shared__ long long s_min;
-    __shared__ int s_bad, s_last;
+    __shared__ int s_bad, s_last, s_nruns;
 
     const int v = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int H = t.H, W = t.W;
@@ -131,13 +208,18 @@ __global__ void __launch_bounds__(PREP_T, 2) prep_kernel(const LT* __restrict__ 
     int bad = ST_OK;
 
     for (int i = tid; i < cap_words; i += PREP_T) bitmap[i] = 0;
+    if (tid == 0) s_nruns = 0;
     __syncthreads();
+    // the run list serves the batch path; the compact-id output needs a pixel pass anyway
+    const bool use_list = !COMPACT_OUT && t.run_cap > 0;
+    uint2* runs = t.runs + (int64_t)v * t.run_cap;
 
     // ---- sweep 1: min / max and the circular presence bitmap (plain read first: almost every bit is already set)
     LT lo = sizeof(LT) == 8 ? (LT)LLONG_MAX : (LT)INT_MAX, hi = sizeof(LT) == 8 ? (LT)LLONG_MIN : (LT)INT_MIN;
+    if (use_list) sweep_mark<LT, VEC>(lab, HW, W, bitmap, cmask, lo, hi, runs, t.run_cap, &s_nruns);
     LT nxt[VEC];
-    load_labels<LT, VEC>(lab, (int64_t)tid * VEC, (int64_t)tid * VEC < HW, nxt);
-    for (int64_t base = 0; base < HW; base += (int64_t)PREP_T * VEC) {
+    if (!use_list) load_labels<LT, VEC>(lab, (int64_t)tid * VEC, (int64_t)tid * VEC < HW, nxt);
+    for (int64_t base = 0; base < HW && !use_list; base += (int64_t)PREP_T * VEC) {
         const int64_t p = base + (int64_t)tid * VEC;
         LT l[VEC];
         const bool in = p < HW;
@@ -217,7 +299,8 @@ __global__ void __launch_bounds__(PREP_T, 2) prep_kernel(const LT* __restrict__ 
             const StatsPtr st{stab, stab + KS_SMEM, stab + 2 * KS_SMEM, stab + 3 * KS_SMEM, stab + 4 * KS_SMEM, 1};
             for (int k = tid; k < K; k += PREP_T) { st.cnt[k] = 0; st.bx0[k] = W; st.by0[k] = H; st.bx1[k] = -1; st.by1[k] = -1; }
             __syncthreads();
-            sweep_runs<LT, VEC, true, COMPACT_OUT>(lab, HW, W, st, rank_of, compact_row);
+            if (use_list && s_nruns <= t.run_cap) sweep_list<true>(runs, s_nruns, st, rank_slot);
+            else sweep_runs<LT, VEC, true, COMPACT_OUT>(lab, HW, W, st, rank_of, compact_row);
             __syncthreads();
             for (int k = tid; k < K; k += PREP_T) {
                 g_cnt[k] = st.cnt[k];
@@ -227,7 +310,8 @@ __global__ void __launch_bounds__(PREP_T, 2) prep_kernel(const LT* __restrict__ 
             const StatsPtr st{g_cnt, g_bb, g_bb + 1, g_bb + 2, g_bb + 3, 4};
             for (int k = tid; k < K; k += PREP_T) { g_cnt[k] = 0; g_bb[4 * k] = W; g_bb[4 * k + 1] = H; g_bb[4 * k + 2] = -1; g_bb[4 * k + 3] = -1; }
             __syncthreads();
-            sweep_runs<LT, VEC, false, COMPACT_OUT>(lab, HW, W, st, rank_of, compact_row);
+            if (use_list && s_nruns <= t.run_cap) sweep_list<false>(runs, s_nruns, st, rank_slot);
+            else sweep_runs<LT, VEC, false, COMPACT_OUT>(lab, HW, W, st, rank_of, compact_row);
         }
     }
 

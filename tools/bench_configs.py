@@ -1,0 +1,90 @@
+#!/usr/bin/env python
+"""Times the other BASELINE.json configs (2: 64 x 224^2 rectangles, 3: 256 x 512^2 Voronoi "SLIC-style", 4: 256 x 224^2 with
+8 label maps per image) through the C ABI with inputs resident in HBM, and spot-checks each against the CPU oracle.
+One JSON line per config.  Not the driver's bench (bench.py is); it shows how the kernels behave off the headline workload."""
+import ctypes as C
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def run(name, images, labels, sizes, pool_reps, steps=10):
+    import torch
+    from image_compression_cpp_b200 import reward
+    from oracle import oracle as orc
+    dev = torch.device("cuda:0")
+    L = reward.lib()
+    multi = labels.ndim == 4
+    S = labels.shape[1] if multi else 1
+    # tile a pool of distinct images up to the config's batch size
+    images_t = np.tile(images, (pool_reps, 1, 1, 1))
+    labels_t = np.tile(labels, (pool_reps,) + (1,) * (labels.ndim - 1))
+    sizes_t = np.tile(sizes, pool_reps)
+    B, _, H, W = images_t.shape
+    ti, tl, ts = (torch.from_numpy(a).to(dev) for a in (images_t, labels_t, sizes_t))
+    K = [len(np.unique(l)) for l in labels.reshape(-1, H, W)[:32]]
+    ws = reward.Workspace(dev, B * S, H, W, Kmax=2048)
+    prm = reward.make_params()
+    out = torch.empty(B * S, dtype=torch.float64, device=dev)
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+    def step():
+        rc = L.icr_compute_rewards(C.c_void_p(ti.data_ptr()), C.c_void_p(tl.data_ptr()), 0, C.c_void_p(ts.data_ptr()), B, S, H, W,
+                                   C.byref(prm), C.c_void_p(out.data_ptr()), ws.handle, st)
+        assert rc == 0, L.icr_last_error()
+    for _ in range(3):
+        step()
+    ws.check()
+    torch.cuda.synchronize()
+    L.icr_workspace_set_profile(ws.handle, 1)
+    kms = np.zeros((steps, 4), np.float32)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(steps):
+        step()
+        L.icr_profile_read(ws.handle, kms[i].ctypes.data_as(C.c_void_p))
+    e1.record()
+    torch.cuda.synchronize()
+    L.icr_workspace_set_profile(ws.handle, 0)
+    k = kms.mean(0)
+    ms = float(k.sum())
+    # spot parity on the first maps
+    n = min(4, images.shape[0])
+    if multi:
+        want = orc.compute_rewards(np.repeat(images[:n], S, axis=0), labels[:n].reshape(n * S, H, W), np.repeat(sizes[:n], S))
+    else:
+        want = orc.compute_rewards(images[:n], labels[:n], sizes[:n])
+    got = out.cpu().numpy()[:want.size]
+    err = float(np.max(np.abs(got - want) / np.abs(want)))
+    px_bytes = 12 + 4 * S
+    alg = B * (H * W * px_bytes + S * (np.mean(K) * 28 + 16))
+    print(json.dumps({"config": name, "images": B, "label_maps": B * S, "H": H, "W": W, "mean_K": float(np.mean(K)),
+                      "ms_per_step_kernels": ms, "images_per_sec": B / (ms * 1e-3), "rewards_per_sec": B * S / (ms * 1e-3),
+                      "kernel_ms": {"prep": float(k[0]), "estimate": float(k[1]), "big": float(k[2]), "reward": float(k[3])},
+                      "algorithmic_GBps": alg / (ms * 1e-3) / 1e9, "max_rel_err_vs_oracle": err}))
+    assert err < 1e-5, err
+    ws.close()
+
+
+def main():
+    from image_compression_cpp_b200 import synth
+    which = sys.argv[1:] or ["2", "3", "4"]
+    if "2" in which:
+        im, lab, sz = synth.make_batch(2)
+        run("cfg2: 64 x 224x224, BSP rectangles", im, lab, sz, 1)
+    if "3" in which:
+        im, lab, sz = synth.make_batch(3, B=32)
+        run("cfg3: 256 x 512x512, Voronoi (SLIC-style) ~1024 segments", im, lab, sz, 8)
+    if "4" in which:
+        im, lab, sz = synth.make_multi_batch(B=32, S=8)
+        run("cfg4: 256 x 224x224, 8 label maps per image (rectangles / region growing)", im, lab, sz, 8)
+
+
+if __name__ == "__main__":
+    main()
