@@ -233,7 +233,7 @@ __device__ void warp_segment(const float* __restrict__ img, const LT* __restrict
             uint32_t left = trow[-1], ul = urow[-1];
             uint32_t l_lo = unpack_lo(left), l_hi = unpack_hi(left), ul_lo = unpack_lo(ul), ul_hi = unpack_hi(ul);
             uint32_t cur = trow[0], up = urow[0];
-#pragma unroll 2
+#pragma unroll 4
             for (int i = 0; i < n; ++i) {
                 // next pixel's loads first: they do not depend on this pixel's stores (one word past the strip is readable)
                 const uint32_t ncur = trow[i + 1], nup = urow[i + 1];
@@ -276,7 +276,7 @@ __device__ void warp_segment(const float* __restrict__ img, const LT* __restrict
             if (f == 3) { pred = par; step = 1; }
             if (f == 4) { pred = ppr; step = 1; }
             uint32_t cur = trow[0], pr = *pred;
-#pragma unroll 2
+#pragma unroll 4
             for (int i = 0; i < n; ++i) {
                 pred += step;
                 const uint32_t ncur = trow[i + 1], npr = *pred;      // loads of the next pixel ahead of this pixel's reductions
@@ -298,7 +298,7 @@ __device__ void warp_segment(const float* __restrict__ img, const LT* __restrict
     double acc = 0.0;
     uint4* h4 = reinterpret_cast<uint4*>(hist) + lane * 8;
     if (npx < (uint32_t)CLOG2_N) {               // no bin can lie beyond the c*log2(c) table: branch-free lookups (tab[0] = 0)
-#pragma unroll 2
+#pragma unroll 4
         for (int j = 0; j < 8; ++j) {
             const uint4 q = h4[j];
             h4[j] = make_uint4(0, 0, 0, 0);
