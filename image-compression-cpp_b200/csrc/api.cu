@@ -320,6 +320,54 @@ int icr_slice_segment(icr_workspace* ws, int v, int k, uint8_t* out_hw4, size_t 
     return ICR_OK;
 }
 
+int icr_slices_prepare(const float* images, const void* labels, int label_dtype, int B, int S, int H, int W, icr_workspace* ws,
+                       icr_stream stream) {
+    if (!images || !labels) return fail(ICR_EINVAL, "null ptr");
+    if (label_dtype != ICR_LABELS_I32 && label_dtype != ICR_LABELS_I64) return fail(ICR_EINVAL, "labels must be int32 or int64");
+    if (B <= 0 || S <= 0) return fail(ICR_EINVAL, "B and S must be positive");
+    if (int rc = check_shape(ws, B * S, H, W)) return rc;
+    Tables t = ws->t;
+    t.V = B * S;
+    ws->in = Inputs{images, labels, label_dtype, S};
+    ws->t.V = t.V;
+    ICR_CUDA(launch_prep(labels, label_dtype, t, nullptr, (cudaStream_t)stream), "prep");
+    return ICR_OK;
+}
+
+int icr_slices_plan(icr_workspace* ws, unsigned long long* offsets_dev, long long capacity, unsigned long long* summary_dev,
+                    icr_stream stream) {
+    if (!ws || !offsets_dev || !summary_dev) return fail(ICR_EINVAL, "null ptr");
+    if (capacity < 1) return fail(ICR_EINVAL, "offsets capacity must be at least 1");
+    if (!ws->in.labels) return fail(ICR_EINVAL, "no batch call has run on this workspace");
+    ICR_CUDA(launch_slice_plan(ws->t, offsets_dev, capacity, summary_dev, (cudaStream_t)stream), "slice plan");
+    return ICR_OK;
+}
+
+int icr_slices_emit(icr_workspace* ws, const unsigned long long* offsets_dev, uint8_t* out_dev, size_t out_capacity, int order,
+                    icr_stream stream) {
+    if (!ws || !offsets_dev || !out_dev) return fail(ICR_EINVAL, "null ptr");
+    if (order != ICR_ORDER_PLANES && order != ICR_ORDER_SWAPPED) return fail(ICR_EINVAL, "order must be ICR_ORDER_PLANES or ICR_ORDER_SWAPPED");
+    if (!ws->in.images) return fail(ICR_EINVAL, "no batch call with images has run on this workspace");
+    ICR_CUDA(launch_slice_emit(ws->t, ws->in, offsets_dev, out_dev, out_capacity, order == ICR_ORDER_SWAPPED, (cudaStream_t)stream),
+             "slice emit");
+    return ICR_OK;
+}
+
+int icr_reassemble_map(icr_workspace* ws, int v, const unsigned long long* offsets_dev, const uint8_t* slices_dev,
+                       uint8_t* canvas_hw4, icr_stream stream) {
+    if (!ws || !offsets_dev || !slices_dev || !canvas_hw4) return fail(ICR_EINVAL, "null ptr");
+    if (v < 0 || v >= ws->t.V) return fail(ICR_EINVAL, "label map index out of range");
+    ICR_CUDA(launch_reassemble(ws->t, v, offsets_dev, slices_dev, canvas_hw4, (cudaStream_t)stream), "reassemble");
+    return ICR_OK;
+}
+
+int icr_paste_slice(uint8_t* canvas_hw4, int W, int H, const uint8_t* slice_hw4, int x, int y, int w, int h, icr_stream stream) {
+    if (!canvas_hw4 || !slice_hw4) return fail(ICR_EINVAL, "null ptr");
+    if (W <= 0 || H <= 0 || w <= 0 || h <= 0 || x < 0 || y < 0) return fail(ICR_EINVAL, "bad slice or canvas geometry");
+    ICR_CUDA(launch_paste(canvas_hw4, W, H, slice_hw4, x, y, w, h, (cudaStream_t)stream), "paste");
+    return ICR_OK;
+}
+
 int icr_ema_update(const double* rewards, int n, const double* sum_count, double momentum, double* state,
                    double* advantages, icr_stream stream) {
     if (!rewards || !state) return fail(ICR_EINVAL, "null ptr");

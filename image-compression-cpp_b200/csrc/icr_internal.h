@@ -82,6 +82,13 @@ cudaError_t launch_big_debug(const Tables& t, const Inputs& in, const EstParams&
                              uint8_t* filter_id, uint32_t* hist, unsigned long long* match,
                              double* size_out, cudaStream_t st);
 cudaError_t launch_slice(const Tables& t, const Inputs& in, int v, int k, uint8_t* out, size_t cap, cudaStream_t st);
+cudaError_t launch_slice_plan(const Tables& t, unsigned long long* offsets, long long capacity, unsigned long long* summary,
+                              cudaStream_t st);
+cudaError_t launch_slice_emit(const Tables& t, const Inputs& in, const unsigned long long* offsets, uint8_t* out, size_t cap,
+                              int swap, cudaStream_t st);
+cudaError_t launch_reassemble(const Tables& t, int v, const unsigned long long* offsets, const uint8_t* slices, uint8_t* canvas,
+                              cudaStream_t st);
+cudaError_t launch_paste(uint8_t* canvas, int W, int H, const uint8_t* slice, int x, int y, int w, int h, cudaStream_t st);
 cudaError_t launch_compact_stats(const int64_t* labels, int H, int W, int K, int32_t* counts,
                                  int32_t* bboxes, cudaStream_t st);
 cudaError_t launch_single_segment(const uint8_t* img, int W, int H, int channels, const int64_t* labels,

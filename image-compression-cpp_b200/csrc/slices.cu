@@ -1,0 +1,186 @@
+// Slice materialisation for the whole batch and the decoder's paste.
+// The reference makes K full-image passes per image on the CPU: (mask == label) then a bbox scan then a masked crop
+// (src/image_slicer.cpp:48-74, one std::async per label at :98-100).  Here the counts and bboxes of the batch are
+// already in the workspace tables, so one launch plans where every slice goes in one packed buffer and one launch
+// writes all of them; the decoder side pastes slices where alpha > 0 (src/reassemble.cpp:75-107).
+#include "icr_internal.h"
+#include "icr_pixel.cuh"
+
+namespace icr {
+
+constexpr int PLAN_T = 1024;
+constexpr int EMIT_T = 128;
+
+// ---- plan: offsets[f] = byte offset of the slice of flat segment f = seg_prefix[v] + k, in (v, k) order;
+// summary = {segments, total bytes}.  One CTA: a batch has tens of thousands of segments, not millions.
+__global__ void __launch_bounds__(PLAN_T) slice_plan_kernel(Tables t, unsigned long long* __restrict__ offsets, long long capacity,
+                                                             unsigned long long* __restrict__ summary) {
+    __shared__ unsigned long long s_warp[PLAN_T / 32];
+    __shared__ unsigned long long s_carry;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int total = t.seg_prefix[t.V];
+    if (tid == 0) s_carry = 0ull;
+    __syncthreads();
+    for (int base = 0; base < total; base += PLAN_T) {
+        const int f = base + tid;
+        unsigned long long a = 0ull;
+        if (f < total) {
+            int lo = 0, hi = t.V - 1;                      // largest v with seg_prefix[v] <= f (maps without segments are skipped over)
+            while (lo < hi) {
+                const int mid = (lo + hi + 1) >> 1;
+                if (t.seg_prefix[mid] <= f) lo = mid; else hi = mid - 1;
+            }
+            const int4 bb = t.bboxes[(int64_t)lo * t.Kmax + (f - t.seg_prefix[lo])];
+            const int w = bb.z - bb.x + 1, h = bb.w - bb.y + 1;
+            if (w > 0 && h > 0) a = 4ull * (unsigned long long)w * (unsigned long long)h;
+        }
+        unsigned long long incl = a;
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned long long up = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += up;
+        }
+        if (lane == 31) s_warp[warp] = incl;
+        __syncthreads();
+        if (warp == 0) {
+            unsigned long long x = s_warp[lane];
+            for (int o = 1; o < 32; o <<= 1) {
+                const unsigned long long up = __shfl_up_sync(0xffffffffu, x, o);
+                if (lane >= o) x += up;
+            }
+            s_warp[lane] = x;                              // inclusive over warps
+        }
+        __syncthreads();
+        const unsigned long long before = s_carry + (warp ? s_warp[warp - 1] : 0ull);
+        if (f < total && (long long)f + 1 < capacity) offsets[f + 1] = before + incl;
+        __syncthreads();
+        if (tid == 0) s_carry += s_warp[PLAN_T / 32 - 1];
+        __syncthreads();
+    }
+    if (tid == 0) {
+        if (capacity > 0) offsets[0] = 0ull;
+        summary[0] = (unsigned long long)total;
+        summary[1] = s_carry;
+    }
+}
+
+// map of flat segment f, found by the 32 lanes together (seg_prefix is ascending)
+__device__ __forceinline__ int map_of_segment(const int32_t* __restrict__ sp, int V, int flat, int lane) {
+    int lo = 0, n = V;
+    while (n > 1) {
+        const int step = (n + 31) >> 5;
+        const int idx = lo + (lane + 1) * step;
+        const bool le = idx < lo + n && __ldg(sp + idx) <= flat;
+        const int c = __popc(__ballot_sync(0xffffffffu, le));
+        lo += c * step;
+        n = min(step, n - c * step);
+    }
+    return lo;
+}
+
+// ---- emit (Rule C + Rule P): one CTA per segment, one warp per slice row, lanes along x; the slice row is contiguous
+// in the packed buffer, so stores are coalesced and the loads are row fragments of the three planes and the label map.
+template <typename LT, bool SWAP>
+__global__ void __launch_bounds__(EMIT_T) slice_emit_kernel(Tables t, Inputs in, const unsigned long long* __restrict__ offsets,
+                                                             uint32_t* __restrict__ out, unsigned long long cap_px) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int total = __ldg(t.seg_prefix + t.V);
+    const int64_t HW = (int64_t)t.H * t.W;
+    for (int flat = blockIdx.x; flat < total; flat += gridDim.x) {
+        const int v = map_of_segment(t.seg_prefix, t.V, flat, lane);
+        const int64_t row = (int64_t)v * t.Kmax + (flat - __ldg(t.seg_prefix + v));
+        const int4 bb = __ldg(t.bboxes + row);
+        const int w = bb.z - bb.x + 1, h = bb.w - bb.y + 1;
+        if (w <= 0 || h <= 0) continue;
+        const unsigned long long o = __ldg(offsets + flat) >> 2;
+        if (o + (unsigned long long)w * h > cap_px) continue;          // the host entry has checked the capacity already
+        const LT key = (LT)__ldg(t.keys + row);
+        const float* __restrict__ img = in.images + (int64_t)(v / in.S) * 3 * HW + (int64_t)bb.y * t.W + bb.x;
+        const LT* __restrict__ lab = static_cast<const LT*>(in.labels) + (int64_t)v * HW + (int64_t)bb.y * t.W + bb.x;
+        uint32_t* __restrict__ dst = out + o;
+        for (int y = warp; y < h; y += EMIT_T / 32) {
+            const int64_t g0 = (int64_t)y * t.W;
+            for (int x = lane; x < w; x += 32) {
+                uint32_t px = 0u;
+                if (lab[g0 + x] == key) {
+                    const float c0 = __ldg(img + g0 + x), c1 = __ldg(img + HW + g0 + x), c2 = __ldg(img + 2 * HW + g0 + x);
+                    px = SWAP ? rgba_of(c2, c1, c0) : rgba_of(c0, c1, c2);
+                }
+                dst[(int64_t)y * w + x] = px;
+            }
+        }
+    }
+}
+
+cudaError_t launch_slice_plan(const Tables& t, unsigned long long* offsets, long long capacity, unsigned long long* summary,
+                              cudaStream_t st) {
+    slice_plan_kernel<<<1, PLAN_T, 0, st>>>(t, offsets, capacity, summary);
+    count_launch();
+    return cudaGetLastError();
+}
+
+cudaError_t launch_slice_emit(const Tables& t, const Inputs& in, const unsigned long long* offsets, uint8_t* out, size_t cap,
+                              int swap, cudaStream_t st) {
+    const int grid = 148 * 16;
+    uint32_t* o = reinterpret_cast<uint32_t*>(out);
+    const unsigned long long cap_px = cap / 4;
+    if (in.label_dtype == ICR_LABELS_I64) {
+        if (swap) slice_emit_kernel<int64_t, true><<<grid, EMIT_T, 0, st>>>(t, in, offsets, o, cap_px);
+        else slice_emit_kernel<int64_t, false><<<grid, EMIT_T, 0, st>>>(t, in, offsets, o, cap_px);
+    } else {
+        if (swap) slice_emit_kernel<int32_t, true><<<grid, EMIT_T, 0, st>>>(t, in, offsets, o, cap_px);
+        else slice_emit_kernel<int32_t, false><<<grid, EMIT_T, 0, st>>>(t, in, offsets, o, cap_px);
+    }
+    count_launch();
+    return cudaGetLastError();
+}
+
+// ---- decoder: paste where alpha > 0 (src/reassemble.cpp:75-107).  All slices of one label map in one launch: the
+// segments of a partition do not overlap, so the order of the pastes does not matter.
+__global__ void __launch_bounds__(EMIT_T) reassemble_kernel(Tables t, int v, const unsigned long long* __restrict__ offsets,
+                                                             const uint32_t* __restrict__ slices, uint32_t* __restrict__ canvas) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int K = t.status[v] == ST_OK ? t.K[v] : 0;
+    const int f0 = t.seg_prefix[v];
+    for (int k = blockIdx.x; k < K; k += gridDim.x) {
+        const int4 bb = t.bboxes[(int64_t)v * t.Kmax + k];
+        const int w = bb.z - bb.x + 1, h = bb.w - bb.y + 1;
+        const uint32_t* __restrict__ src = slices + (offsets[f0 + k] >> 2);
+        for (int y = warp; y < h; y += EMIT_T / 32)
+            for (int x = lane; x < w; x += 32) {
+                const uint32_t px = src[(int64_t)y * w + x];
+                if (px >> 24) canvas[(int64_t)(bb.y + y) * t.W + bb.x + x] = px;
+            }
+    }
+}
+
+// one slice from anywhere (a decoded file), clipped to the canvas as :58-66 does; pastes issued on one stream keep the
+// reference's order, so a later slice wins where two overlap
+__global__ void __launch_bounds__(256) paste_kernel(uint32_t* __restrict__ canvas, int W, int H, const uint32_t* __restrict__ slice,
+                                                     int x0, int y0, int w, int cw, int ch) {
+    for (int y = blockIdx.x * 8 + (threadIdx.x >> 5); y < ch; y += gridDim.x * 8)
+        for (int x = threadIdx.x & 31; x < cw; x += 32) {
+            const uint32_t px = slice[(int64_t)y * w + x];
+            if (px >> 24) canvas[(int64_t)(y0 + y) * W + x0 + x] = px;
+        }
+}
+
+cudaError_t launch_reassemble(const Tables& t, int v, const unsigned long long* offsets, const uint8_t* slices, uint8_t* canvas,
+                              cudaStream_t st) {
+    cudaError_t e = cudaMemsetAsync(canvas, 0, (size_t)t.H * t.W * 4, st);        // cv::Scalar(0,0,0,0), :50
+    if (e != cudaSuccess) return e;
+    reassemble_kernel<<<148 * 4, EMIT_T, 0, st>>>(t, v, offsets, reinterpret_cast<const uint32_t*>(slices),
+                                                   reinterpret_cast<uint32_t*>(canvas));
+    count_launch();
+    return cudaGetLastError();
+}
+
+cudaError_t launch_paste(uint8_t* canvas, int W, int H, const uint8_t* slice, int x, int y, int w, int h, cudaStream_t st) {
+    const int cw = min(w, W - x), ch = min(h, H - y);                              // :58-59
+    if (cw <= 0 || ch <= 0) return cudaSuccess;                                    // "lies outside canvas, skipping", :61-64
+    const int grid = min((ch + 7) / 8, 148 * 4);
+    paste_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<uint32_t*>(canvas), W, H, reinterpret_cast<const uint32_t*>(slice), x, y, w, cw, ch);
+    count_launch();
+    return cudaGetLastError();
+}
+
+}  // namespace icr

@@ -29,7 +29,7 @@ SYMBOLS = ["icr_last_error", "icr_version", "icr_default_params", "icr_workspace
            "icr_workspace_destroy", "icr_compute_rewards", "icr_compute_rewards_host", "icr_check",
            "icr_label_capacity", "icr_segment_stats", "icr_counts_bboxes_from_compact_labels",
            "icr_estimate_png_size_segment", "icr_workspace_tables", "icr_debug_segment", "icr_slice_segment",
-           "icr_ema_update", "icr_reward_sum_count", "icr_selftest", "icr_launch_count", "icr_workspace_set_profile",
+           "icr_slices_prepare", "icr_slices_plan", "icr_slices_emit", "icr_reassemble_map", "icr_paste_slice", "icr_ema_update", "icr_reward_sum_count", "icr_selftest", "icr_launch_count", "icr_workspace_set_profile",
            "icr_profile_read"]
 
 
@@ -142,6 +142,27 @@ class Workspace:
         with torch.cuda.device(self.device):
             _check(lib().icr_slice_segment(self._h, C.c_int(v), C.c_int(k), _ptr(out), C.c_size_t(out.numel()), _stream()))
         return out
+
+    def slices(self, order=0):
+        """All slices of the last batch call in one packed device buffer (src/image_slicer.cpp:81-125 for the whole batch).
+        Returns (buffer u8 [total bytes], offsets int64 [segments + 1]); slice f = (segments of earlier maps) + k is
+        buffer[offsets[f]:offsets[f+1]] viewed as [h,w,4].  One 16-byte read-back sizes the buffer."""
+        dev = self.device
+        offsets = torch.zeros(self.V * self.Kmax + 1, dtype=torch.int64, device=dev)
+        summary = torch.zeros(2, dtype=torch.int64, device=dev)
+        with torch.cuda.device(dev):
+            _check(lib().icr_slices_plan(self._h, _ptr(offsets), C.c_longlong(offsets.numel()), _ptr(summary), _stream()))
+            nseg, nbytes = (int(x) for x in summary.tolist())
+            buf = torch.empty(max(nbytes, 4), dtype=torch.uint8, device=dev)
+            _check(lib().icr_slices_emit(self._h, _ptr(offsets), _ptr(buf), C.c_size_t(nbytes), C.c_int(order), _stream()))
+        return buf[:nbytes], offsets[:nseg + 1]
+
+    def reassemble_map(self, v, buf, offsets):
+        """Decoder check (src/reassemble.cpp:50-107): canvas u8 [H,W,4] with every slice of map v pasted where alpha > 0."""
+        canvas = torch.empty((self.H, self.W, 4), dtype=torch.uint8, device=self.device)
+        with torch.cuda.device(self.device):
+            _check(lib().icr_reassemble_map(self._h, C.c_int(v), _ptr(offsets), _ptr(buf), _ptr(canvas), _stream()))
+        return canvas
 
     def close(self):
         if self._h:
@@ -329,6 +350,16 @@ class EMABaseline:
             _check(lib().icr_ema_update(_ptr(r), C.c_int(r.numel()), _ptr(sum_count) if sum_count is not None else None,
                                         C.c_double(self.momentum), _ptr(self.state), _ptr(adv) if advantages else None, _stream()))
         return (self.state[0], adv.view_as(rewards)) if advantages else self.state[0]
+
+
+def paste_slice(canvas, slice_hw4, x, y):
+    """canvas u8 [H,W,4] (CUDA) receives slice u8 [h,w,4] at (x, y) where the slice's alpha > 0, clipped to the canvas."""
+    H, W = canvas.shape[:2]
+    h, w = slice_hw4.shape[:2]
+    with torch.cuda.device(canvas.device):
+        _check(lib().icr_paste_slice(_ptr(canvas), C.c_int(W), C.c_int(H), _ptr(slice_hw4.contiguous()), C.c_int(x), C.c_int(y),
+                                     C.c_int(w), C.c_int(h), _stream()))
+    return canvas
 
 
 def reward_sum_count(rewards):

@@ -130,6 +130,34 @@ int icr_debug_segment(icr_workspace* ws, int v, int k, const icr_params* params,
 int icr_slice_segment(icr_workspace* ws, int v, int k, uint8_t* out_hw4, size_t out_capacity,
                       icr_stream stream);
 
+/* ---- all slices of the last icr_compute_rewards batch in one packed buffer: what write_slices materialises one label at
+ * a time on the CPU (src/image_slicer.cpp:81-125: K x {full-image mask, bbox scan, masked crop}).  Flat segment
+ * f = (segments of the maps before v) + k, maps and compact ids ascending -- within a map that is ascending label value.
+ * icr_slices_plan: offsets_dev u64 [capacity] receives the byte offset of slice f at [f] and the end at [segments];
+ * summary_dev u64 [2] = {segments, total bytes}.  The caller reads summary back, sizes the buffer, then
+ * icr_slices_emit writes slice f as u8 [h,w,4] at offsets[f]: (c0,c1,c2,255) inside the segment, (0,0,0,0) outside.
+ * order: ICR_ORDER_PLANES keeps the plane order, ICR_ORDER_SWAPPED writes (c2,c1,c0,255) -- BGRA from RGB planes, the
+ * cv::Mat layout of src/compress.cpp:145.  The caller's images and labels of that batch call must still be alive.
+ * icr_slices_prepare runs only the label pass (Rules L and S) for a batch and records its buffers, for callers that
+ * want slices without rewards (the `compress` executable, src/compress.cpp:138-147); follow it with icr_check. */
+#define ICR_ORDER_PLANES 0
+#define ICR_ORDER_SWAPPED 1
+int icr_slices_prepare(const float* images_b3hw, const void* labels_vhw, int label_dtype, int B, int S, int H, int W,
+                       icr_workspace* ws, icr_stream stream);
+int icr_slices_plan(icr_workspace* ws, unsigned long long* offsets_dev, long long capacity,
+                    unsigned long long* summary_dev, icr_stream stream);
+int icr_slices_emit(icr_workspace* ws, const unsigned long long* offsets_dev, uint8_t* out_dev, size_t out_capacity,
+                    int order, icr_stream stream);
+
+/* ---- decoder side (src/reassemble.cpp:50-107): canvas u8 [H,W,4] starts at (0,0,0,0) and receives a slice where its
+ * alpha > 0.  icr_reassemble_map clears the canvas and pastes every slice of label map v of the planned buffer in one
+ * launch; icr_paste_slice pastes one slice from anywhere (a decoded file), clipped to the canvas, and leaves the rest of
+ * the canvas alone -- pastes issued on one stream keep the reference's sequential order. */
+int icr_reassemble_map(icr_workspace* ws, int v, const unsigned long long* offsets_dev, const uint8_t* slices_dev,
+                       uint8_t* canvas_hw4, icr_stream stream);
+int icr_paste_slice(uint8_t* canvas_hw4, int W, int H, const uint8_t* slice_hw4, int x, int y, int w, int h,
+                    icr_stream stream);
+
 /* ---- Rule E + advantage (include/ema_baseline.hpp:11-21, src/fcn/training.cpp:178-181).
  * state (device, 2 doubles): {value, initialized flag}.  sum_count (device, 2 doubles) holds the
  * global {sum of rewards, count} -- after an all-reduce when the batch is sharded; pass NULL to

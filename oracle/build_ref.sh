@@ -8,6 +8,12 @@ REF="${REF:-/root/reference}"
 OUT="$HERE/_ref"
 [ -d "$REF/src" ] || { echo "no reference at $REF; keeping prebuilt $OUT" >&2; exit 0; }
 mkdir -p "$OUT"
+# the sidecar writer/reader: one plain C++ file, seconds (the stdexcept include is the only thing it lacks on this compiler)
+if [ ! -f "$OUT/libref_metadata.so" ] || [ "$HERE/ref_metadata_shim.cpp" -nt "$OUT/libref_metadata.so" ]; then
+  g++ -std=c++17 -O2 -fPIC -shared -include stdexcept -I"$REF/include" "$REF/src/metadata.cpp" "$HERE/ref_metadata_shim.cpp" \
+    -o "$OUT/libref_metadata.so"
+  echo "built $OUT/libref_metadata.so"
+fi
 TORCH="$(python -c 'import torch,os;print(os.path.dirname(torch.__file__))')"
 INC="-I$REF/include -I$TORCH/include -I$TORCH/include/torch/csrc/api/include"
 NVF="-std=c++17 -O3 -gencode arch=compute_100a,code=sm_100a -D_GLIBCXX_USE_CXX11_ABI=1 --expt-relaxed-constexpr -Xcompiler -fPIC"

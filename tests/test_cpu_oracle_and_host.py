@@ -169,6 +169,7 @@ sc = torch.tensor([float(local.sum()), float(local.numel())], dtype=torch.float6
 g, tot = sharding.exchange(local, sc, B)
 assert torch.equal(g, allr), (g, allr)
 assert tot.tolist() == [float(allr.sum()), float(B)]
+assert torch.equal(sharding.gather_rewards(local, B), allr)
 if rank == 0:
     print("OK", float(tot[0] / tot[1]))
 dist.destroy_process_group()
