@@ -21,31 +21,23 @@
 #include <string>
 #include <tuple>
 
-#include "../../include/icr_b200.h"
+#include "host_internal.hpp"
 #include "include/compute_rewards.cuh"
 #include "include/ema_baseline.hpp"
 #include "include/png_size_estimator.cuh"
 #include "include/rama_handoff.hpp"
 #include "include/segment_stats.cuh"
 
-namespace {
+using icrh::WsHolder;
+using icrh::current_stream;
+using icrh::label_code;
+using icrh::throw_runtime;
+using icrh::workspace_for;
 
-icr_stream current_stream() { return (icr_stream)c10::cuda::getCurrentCUDAStream().stream(); }
-
-[[noreturn]] void throw_runtime() { throw std::runtime_error(icr_last_error()); }
-
-// ---- grow-only workspace cache, one per (host thread, device, H, W): the role of the reference's
-// thread_local PngEstimatorWorkspace table (src/png_size_estimator.cu:466-469)
-struct WsHolder {
-    icr_workspace* ws = nullptr;
-    int V = 0, Kmax = 0;
-    ~WsHolder() { if (ws) icr_workspace_destroy(ws); }
-};
+namespace icrh {
 
 using WsKey = std::tuple<int, int, int>;
 thread_local std::map<WsKey, std::unique_ptr<WsHolder>> g_ws;
-
-constexpr int KMAX_FIRST = 2048;   // table rows per label map to start with; grown to H*W on demand
 
 WsHolder& workspace_for(int device, int V, int H, int W, int Kmax) {
     auto& slot = g_ws[WsKey(device, H, W)];
@@ -67,7 +59,12 @@ WsHolder& workspace_for(int device, int V, int H, int W, int Kmax) {
     return h;
 }
 
-int label_code(const torch::Tensor& t) { return t.scalar_type() == torch::kInt64 ? ICR_LABELS_I64 : ICR_LABELS_I32; }
+}  // namespace icrh
+
+namespace {
+
+using icrh::KMAX_FIRST;
+
 
 icr_params make_params(int32_t min_pixels, int L_min, float beta, float token, float gamma, double overhead, bool adaptive,
                        double lambda) {
@@ -296,13 +293,9 @@ std::pair<torch::Tensor, torch::Tensor> EMABaseline::update_with_advantages(cons
 // functions above.
 namespace {
 thread_local std::string g_hook_err;
-template <class F> int guarded(F&& f) {
-    try { f(); return 0; }
-    catch (const c10::Error& e) { g_hook_err = e.what_without_backtrace(); return 1; }
-    catch (const std::exception& e) { g_hook_err = e.what(); return 2; }
-    catch (...) { g_hook_err = "unknown exception"; return 3; }
-}
 }  // namespace
+namespace icrh { void set_hook_error(const std::string& e) { g_hook_err = e; } }
+using icrh::guarded;
 
 extern "C" {
 

@@ -162,3 +162,64 @@ def test_cpp_multi_map_entry_and_ema(host, orc, dev):
     assert host.icrh_ema_step(_p(out), 6, 0, C.c_double(0.99), state, None) == 0
     v2, _ = orc.ema_update(v1, True, 0.99, got)
     assert abs(state[0] - v2) < 1e-12
+
+
+# ---- the rows after the reward path: write_slices + metadata.bin + reassemble
+def test_host_library_exports_the_slice_and_decoder_surface():
+    out = subprocess.check_output(["nm", "-DC", "--defined-only", HOST_LIB], text=True)
+    for sig in ("write_metadata_binary(std::vector<SliceMetadata, std::allocator<SliceMetadata> > const&, std::__cxx11::basic_string<char, std::char_traits<char>, std::allocator<char> > const&, unsigned int, unsigned int)",
+                "read_metadata_binary(std::__cxx11::basic_string<char, std::char_traits<char>, std::allocator<char> > const&, unsigned int&, unsigned int&)",
+                "write_slices(at::Tensor const&, at::Tensor const&, std::filesystem::__cxx11::path const&, std::filesystem::__cxx11::path const&)",
+                "reassemble(std::filesystem::__cxx11::path, std::filesystem::__cxx11::path)",
+                "slice_images_batched(at::Tensor const&, at::Tensor const&, bool)"):
+        assert sig in out, sig
+
+
+def test_cpp_metadata_writer_produces_the_reference_bytes(host, tmp_path):
+    """No GPU involved: the C++ writer against the bytes src/metadata.cpp itself wrote (tests/golden/metadata_ref.bin)."""
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "tests", "golden"))
+    import make_metadata_golden as g
+    cols = [np.array([r[i] for r in g.RECORDS], np.int32) for i in (0, 2, 3, 4, 5)]
+    names = b"".join(r[1].encode() + b"\0" for r in g.RECORDS)
+    path = str(tmp_path / "metadata.bin").encode()
+    assert host.icrh_write_metadata(path, len(g.RECORDS), *[c.ctypes.data_as(C.c_void_p) for c in cols], names,
+                                    C.c_uint32(g.IMAGE_W), C.c_uint32(g.IMAGE_H)) == 0, host.icrh_last_error()
+    assert open(path, "rb").read() == open(os.path.join(ROOT, "tests", "golden", "metadata_ref.bin"), "rb").read()
+    iw, ih = C.c_uint32(), C.c_uint32()
+    assert host.icrh_read_metadata_count(path, C.byref(iw), C.byref(ih)) == len(g.RECORDS) and (iw.value, ih.value) == (g.IMAGE_W, g.IMAGE_H)
+    bad = tmp_path / "bad.bin"
+    bad.write_bytes(b"\0" * 32)
+    assert host.icrh_read_metadata_count(str(bad).encode(), C.byref(iw), C.byref(ih)) == -2 and b"magic mismatch" in host.icrh_last_error()
+    assert host.icrh_read_metadata_count(str(tmp_path / "none.bin").encode(), C.byref(iw), C.byref(ih)) == -2
+    assert b"Cannot open" in host.icrh_last_error()
+
+
+@pytest.mark.gpu
+def test_cpp_write_slices_files_and_reassemble_round_trip(host, orc, dev, tmp_path):
+    from PIL import Image
+    from oracle import slices_oracle as so
+    H, W = 64, 88
+    image = synth.image_f32_chw(1, H, W, 21)
+    mask = synth.bfs_partition(H, W, 10, seed=6).astype(np.int32)
+    ti, tm = _dev(image, mask)
+    assert host.icrh_write_slices(_p(ti), _p(tm), 0, H, W, 0, str(tmp_path).encode(), b"img0") == 0, host.icrh_last_error()
+    d = tmp_path / "img0"
+    rgba = orc.chw3_f32_to_rgba(image)
+    recs = so.write_slices(rgba, mask)
+    assert (d / "metadata.bin").read_bytes() == so.metadata_bytes(recs, W, H)             # ascending labels, slice_<label>.png
+    for label, name, x, y, w, h, sl in recs:
+        assert np.array_equal(np.asarray(Image.open(d / name).convert("RGBA")), sl), name
+    canvas = torch.zeros((H, W, 4), dtype=torch.uint8, device="cuda")
+    out_png = tmp_path / "reconstructed.png"
+    assert host.icrh_reassemble(str(d).encode(), str(out_png).encode(), 0, _p(canvas), H, W) == 0, host.icrh_last_error()
+    assert np.array_equal(canvas.cpu().numpy(), rgba)
+    assert np.array_equal(np.asarray(Image.open(out_png).convert("RGBA")), rgba)
+    # the decoder reads files other encoders wrote too (RGB without alpha, every PNG filter type)
+    x, y, w, h = recs[0][2:6]
+    Image.fromarray(rgba[y:y + h, x:x + w, :3]).save(d / recs[0][1], optimize=True)
+    assert host.icrh_reassemble(str(d).encode(), None, 0, _p(canvas), H, W) == 0, host.icrh_last_error()
+    # that file is now opaque everywhere: its whole bbox is pasted first, the other slices land on top of it
+    assert np.array_equal(canvas.cpu().numpy(), rgba)
+    assert host.icrh_reassemble(str(tmp_path / "nothing").encode(), None, 0, _p(canvas), H, W) == 2
+    assert b"Cannot open metadata file" in host.icrh_last_error()
