@@ -34,7 +34,7 @@ static int cuda_fail(cudaError_t e, const char* what) {
 
 static size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
 
-struct Layout { size_t K, status, counts, bboxes, keys, sizes, err, seg_prefix, sched, big_filter, clog2, runs, total; };
+struct Layout { size_t K, status, counts, bboxes, keys, sizes, err, seg_prefix, sched, big_filter, clog2, runs, slice_map_off, total; };
 
 static Layout layout(int V, int H, int W, int Kmax) {
     Layout l; size_t o = 0;
@@ -50,6 +50,7 @@ static Layout layout(int V, int H, int W, int Kmax) {
     l.big_filter = o; o = align_up(o + (size_t)V * BIG_CTAS * H);
     l.clog2 = o; o = align_up(o + (size_t)CLOG2_N * 8);
     l.runs = o; o = align_up(o + (size_t)V * run_capacity(H, W) * 8);
+    l.slice_map_off = o; o = align_up(o + (size_t)V * 8);
     l.total = o;
     return l;
 }
@@ -117,6 +118,7 @@ int icr_workspace_create(icr_workspace** out, int device, int V, int H, int W, i
     t.err = (int32_t*)(ws->base + l.err); t.big_filter = (uint8_t*)(ws->base + l.big_filter); t.clog2 = (const double*)(ws->base + l.clog2);
     t.V = V; t.H = H; t.W = W; t.Kmax = Kmax;
     t.runs = (uint2*)(ws->base + l.runs); t.run_cap = run_capacity(H, W);
+    t.slice_map_off = (unsigned long long*)(ws->base + l.slice_map_off);
     std::vector<double> tab(CLOG2_N);
     tab[0] = 0.0;
     for (int c = 1; c < CLOG2_N; ++c) tab[c] = (double)c * std::log2((double)c);

@@ -25,6 +25,7 @@ struct Tables {            // device pointers into the workspace, V label maps
     uint8_t* big_filter;   // [V*BIG_CTAS, H] filter ids of the segment a big-kernel CTA is working on
     uint2* runs;           // [V, run_cap] label runs of a map found by prep's first sweep {slot | (len-1)<<20, y<<16 | x}
     int run_cap;           // 0 = no run list (very wide maps)
+    unsigned long long* slice_map_off;   // [V] byte offset of a map's first slice in the packed slice buffer (slices.cu)
     const double* clog2;   // [CLOG2_N] c*log2(c)
     int V, H, W, Kmax;
 };

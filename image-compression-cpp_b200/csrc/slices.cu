@@ -12,54 +12,70 @@ constexpr int PLAN_T = 1024;
 constexpr int EMIT_T = 128;
 
 // ---- plan: offsets[f] = byte offset of the slice of flat segment f = seg_prefix[v] + k, in (v, k) order;
-// summary = {segments, total bytes}.  One CTA: a batch has tens of thousands of segments, not millions.
-__global__ void __launch_bounds__(PLAN_T) slice_plan_kernel(Tables t, unsigned long long* __restrict__ offsets, long long capacity,
-                                                             unsigned long long* __restrict__ summary) {
+// summary = {segments, total bytes}.  Three small launches: bytes per map (a warp per map), a scan over the maps
+// (one CTA), and the offsets inside each map (a warp per map).
+__device__ __forceinline__ unsigned long long slice_bytes_of(const int4 bb) {
+    const int w = bb.z - bb.x + 1, h = bb.w - bb.y + 1;
+    return (w > 0 && h > 0) ? 4ull * (unsigned long long)w * (unsigned long long)h : 0ull;
+}
+
+__device__ __forceinline__ unsigned long long warp_inclusive(unsigned long long x, int lane) {
+    for (int o = 1; o < 32; o <<= 1) {
+        const unsigned long long up = __shfl_up_sync(0xffffffffu, x, o);
+        if (lane >= o) x += up;
+    }
+    return x;
+}
+
+__global__ void __launch_bounds__(256) plan_map_bytes_kernel(Tables t, unsigned long long* __restrict__ map_off) {
+    const int v = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (v >= t.V) return;
+    const int K = t.seg_prefix[v + 1] - t.seg_prefix[v];               // 0 for a map that failed
+    unsigned long long a = 0ull;
+    for (int k = lane; k < K; k += 32) a += slice_bytes_of(__ldg(t.bboxes + (int64_t)v * t.Kmax + k));
+    for (int o = 16; o; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
+    if (lane == 0) map_off[v] = a;
+}
+
+__global__ void __launch_bounds__(PLAN_T) plan_scan_maps_kernel(Tables t, unsigned long long* __restrict__ map_off,
+                                                                 unsigned long long* __restrict__ summary) {
     __shared__ unsigned long long s_warp[PLAN_T / 32];
     __shared__ unsigned long long s_carry;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int total = t.seg_prefix[t.V];
     if (tid == 0) s_carry = 0ull;
     __syncthreads();
-    for (int base = 0; base < total; base += PLAN_T) {
-        const int f = base + tid;
-        unsigned long long a = 0ull;
-        if (f < total) {
-            int lo = 0, hi = t.V - 1;                      // largest v with seg_prefix[v] <= f (maps without segments are skipped over)
-            while (lo < hi) {
-                const int mid = (lo + hi + 1) >> 1;
-                if (t.seg_prefix[mid] <= f) lo = mid; else hi = mid - 1;
-            }
-            const int4 bb = t.bboxes[(int64_t)lo * t.Kmax + (f - t.seg_prefix[lo])];
-            const int w = bb.z - bb.x + 1, h = bb.w - bb.y + 1;
-            if (w > 0 && h > 0) a = 4ull * (unsigned long long)w * (unsigned long long)h;
-        }
-        unsigned long long incl = a;
-        for (int o = 1; o < 32; o <<= 1) {
-            const unsigned long long up = __shfl_up_sync(0xffffffffu, incl, o);
-            if (lane >= o) incl += up;
-        }
+    for (int base = 0; base < t.V; base += PLAN_T) {
+        const int v = base + tid;
+        const unsigned long long a = v < t.V ? map_off[v] : 0ull;
+        const unsigned long long incl = warp_inclusive(a, lane);
         if (lane == 31) s_warp[warp] = incl;
         __syncthreads();
-        if (warp == 0) {
-            unsigned long long x = s_warp[lane];
-            for (int o = 1; o < 32; o <<= 1) {
-                const unsigned long long up = __shfl_up_sync(0xffffffffu, x, o);
-                if (lane >= o) x += up;
-            }
-            s_warp[lane] = x;                              // inclusive over warps
-        }
+        if (warp == 0) s_warp[lane] = warp_inclusive(s_warp[lane], lane);
         __syncthreads();
-        const unsigned long long before = s_carry + (warp ? s_warp[warp - 1] : 0ull);
-        if (f < total && (long long)f + 1 < capacity) offsets[f + 1] = before + incl;
+        if (v < t.V) map_off[v] = s_carry + (warp ? s_warp[warp - 1] : 0ull) + incl - a;       // exclusive
         __syncthreads();
         if (tid == 0) s_carry += s_warp[PLAN_T / 32 - 1];
         __syncthreads();
     }
     if (tid == 0) {
-        if (capacity > 0) offsets[0] = 0ull;
-        summary[0] = (unsigned long long)total;
+        summary[0] = (unsigned long long)t.seg_prefix[t.V];
         summary[1] = s_carry;
+    }
+}
+
+__global__ void __launch_bounds__(256) plan_offsets_kernel(Tables t, const unsigned long long* __restrict__ map_off,
+                                                           unsigned long long* __restrict__ offsets, long long capacity) {
+    const int v = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (v >= t.V) return;
+    const int f0 = t.seg_prefix[v], K = t.seg_prefix[v + 1] - f0;
+    unsigned long long run = map_off[v];
+    if (v == 0 && lane == 0) offsets[0] = 0ull;
+    for (int k0 = 0; k0 < K; k0 += 32) {
+        const int k = k0 + lane;
+        const unsigned long long a = k < K ? slice_bytes_of(__ldg(t.bboxes + (int64_t)v * t.Kmax + k)) : 0ull;
+        const unsigned long long incl = warp_inclusive(a, lane);
+        if (k < K && (long long)f0 + k + 1 < capacity) offsets[f0 + k + 1] = run + incl;
+        run += __shfl_sync(0xffffffffu, incl, 31);
     }
 }
 
@@ -113,8 +129,11 @@ __global__ void __launch_bounds__(EMIT_T) slice_emit_kernel(Tables t, Inputs in,
 
 cudaError_t launch_slice_plan(const Tables& t, unsigned long long* offsets, long long capacity, unsigned long long* summary,
                               cudaStream_t st) {
-    slice_plan_kernel<<<1, PLAN_T, 0, st>>>(t, offsets, capacity, summary);
-    count_launch();
+    const int grid = (t.V + 7) / 8;
+    plan_map_bytes_kernel<<<grid, 256, 0, st>>>(t, t.slice_map_off);
+    plan_scan_maps_kernel<<<1, PLAN_T, 0, st>>>(t, t.slice_map_off, summary);
+    plan_offsets_kernel<<<grid, 256, 0, st>>>(t, t.slice_map_off, offsets, capacity);
+    count_launch(3);
     return cudaGetLastError();
 }
 
