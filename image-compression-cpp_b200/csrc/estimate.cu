@@ -27,8 +27,14 @@ constexpr int MAXSW = 16;             // widest strip one lane walks
 
 // shared-memory budget per warp.  choose_geometry() only returns geometries whose (R+1) row slots of w+2 words fit TILE_CAP;
 // one row per group (S = 32) always fits: 2 * (EST_MAX_W + 2) <= TILE_CAP.
-constexpr int TILE_CAP = 576;
+constexpr int TILE_CAP = 456;
 constexpr int TILE_WORDS = TILE_CAP + 8;
+constexpr int RAW_BYTES = 4096;                   // async staging window per warp
+template <typename LT> struct RawWindow {
+    static constexpr int parts = 3 + (int)sizeof(LT) / 4;          // 16-byte pieces per quad: r, g, b, labels (two for int64)
+    static constexpr int quads = RAW_BYTES / (16 * parts);         // 64 quads with int32 labels, 51 with int64
+    static constexpr int per_lane = (quads + 31) / 32;
+};
 constexpr int PLANE_WORDS = TILE_CAP;             // R rows x (w|1) words < (R+1) * (w+2)
 static_assert(2 * (EST_MAX_W + 2) <= TILE_CAP, "a single-row group of the widest bbox must fit the tile");
 
@@ -37,6 +43,7 @@ struct __align__(16) WarpSmem {
     uint32_t tile[TILE_WORDS];        // masked RGBA words, (R+1) rolling row slots of (w+1)|1 words
     uint32_t pavg[PLANE_WORDS];       // Avg predictor of the group's pixels
     uint32_t ppae[PLANE_WORDS];       // Paeth predictor
+    uint4 raw[RAW_BYTES / 16];        // the next row group's first quads as they lie in HBM (f32 planes, labels), filled by cp.async
 };
 
 struct DebugOut {
@@ -137,10 +144,11 @@ __device__ __forceinline__ void load_quad(const int64_t* p, int64_t (&l)[4]) {
 
 template <typename LT, bool FULL>
 __device__ __forceinline__ void stage_rows_vec(const float* __restrict__ img, const LT* __restrict__ lab, uint32_t HW, uint32_t base, int W, LT key,
-                                               int w, int dx, int nq, float rnq, int nr, int s0, int R, int tst, uint32_t* tile, int lane) {
+                                               int w, int dx, int nq, float rnq, int nr, int s0, int R, int tst, uint32_t* tile, int lane,
+                                               int qfirst = 0) {
     const int total = nr * nq;
     constexpr int U = 2;                              // quads in flight per lane
-    for (int q0 = lane; q0 < total; q0 += 32 * U) {
+    for (int q0 = qfirst + lane; q0 < total; q0 += 32 * U) {
         float4 r[U], g[U], b[U];
         LT l[U][4];
         int dst[U], xb[U];
@@ -169,6 +177,77 @@ __device__ __forceinline__ void stage_rows_vec(const float* __restrict__ img, co
                 for (int e = 0; e < 4; ++e)
                     if ((unsigned)(xb[u] + e) < (unsigned)w) tile[dst[u] + e] = (FULL || l[u][e] == key) ? px[e] : 0u;
             }
+        }
+    }
+}
+
+// ---- the same staging split in two, so that the memory latency of a row group is spent under the walks of the group
+// before it: raw_request asks the first RawWindow::quads quads of a group into the warp's raw window with cp.async (no
+// registers are held while they fly), raw_convert turns them into tile words once they have landed.  Every lane converts
+// exactly the quads it requested, so the only ordering needed is the lane's own cp.async.wait_group.
+__device__ __forceinline__ void cp_async16(uint32_t saddr, const void* g) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(saddr), "l"(g) : "memory");
+}
+
+template <typename LT>
+__device__ __forceinline__ void raw_request(const float* __restrict__ img, const LT* __restrict__ lab, uint32_t HW, uint32_t base, int W,
+                                            int nq, float rnq, int nr, bool full, uint4* raw, int lane) {
+    using RW = RawWindow<LT>;
+    const int total = min(nr * nq, RW::quads);
+    const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(raw);
+#pragma unroll
+    for (int u = 0; u < RW::per_lane; ++u) {
+        const int q = lane + 32 * u;
+        if (q < total) {
+            const int rr = __float2int_rz(((float)q + 0.5f) * rnq);
+            const uint32_t off = base + (uint32_t)(rr * W + 4 * (q - rr * nq));
+            const uint32_t sa = sbase + 16u * q;
+            cp_async16(sa, img + off);
+            cp_async16(sa + 16u * RW::quads, img + (off + HW));
+            cp_async16(sa + 32u * RW::quads, img + (off + 2u * HW));
+            if (!full) {
+                cp_async16(sa + 48u * RW::quads, lab + off);
+                if (sizeof(LT) == 8) cp_async16(sa + 64u * RW::quads, lab + off + 2);
+            }
+        }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+}
+
+__device__ __forceinline__ void raw_labels(const uint4* raw, int quads, int q, int32_t (&l)[4]) {
+    const uint4 a = raw[3 * quads + q];
+    l[0] = (int32_t)a.x; l[1] = (int32_t)a.y; l[2] = (int32_t)a.z; l[3] = (int32_t)a.w;
+}
+__device__ __forceinline__ void raw_labels(const uint4* raw, int quads, int q, int64_t (&l)[4]) {
+    const uint4 a = raw[3 * quads + q], b = raw[4 * quads + q];
+    l[0] = (int64_t)((uint64_t)a.y << 32 | a.x); l[1] = (int64_t)((uint64_t)a.w << 32 | a.z);
+    l[2] = (int64_t)((uint64_t)b.y << 32 | b.x); l[3] = (int64_t)((uint64_t)b.w << 32 | b.z);
+}
+
+template <typename LT>
+__device__ __forceinline__ void raw_convert(LT key, int w, int dx, int nq, float rnq, int nr, int s0, int R, int tst, bool full,
+                                            const uint4* raw, uint32_t* tile, int lane) {
+    using RW = RawWindow<LT>;
+    const int total = min(nr * nq, RW::quads);
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+#pragma unroll
+    for (int u = 0; u < RW::per_lane; ++u) {
+        const int q = lane + 32 * u;
+        if (q < total) {
+            const int rr = __float2int_rz(((float)q + 0.5f) * rnq);
+            const int xb = 4 * (q - rr * nq) - dx;
+            int slot = s0 + rr; if (slot > R) slot -= R + 1;
+            const int dst = slot * tst + 1 + xb;
+            const uint4 ur = raw[q], ug = raw[RW::quads + q], ub = raw[2 * RW::quads + q];
+            LT l[4] = {key, key, key, key};
+            if (!full) raw_labels(raw, RW::quads, q, l);
+            const uint32_t px[4] = {rgba_of(__uint_as_float(ur.x), __uint_as_float(ug.x), __uint_as_float(ub.x)),
+                                    rgba_of(__uint_as_float(ur.y), __uint_as_float(ug.y), __uint_as_float(ub.y)),
+                                    rgba_of(__uint_as_float(ur.z), __uint_as_float(ug.z), __uint_as_float(ub.z)),
+                                    rgba_of(__uint_as_float(ur.w), __uint_as_float(ug.w), __uint_as_float(ub.w))};
+#pragma unroll
+            for (int e = 0; e < 4; ++e)
+                if ((unsigned)(xb + e) < (unsigned)w) tile[dst + e] = l[e] == key ? px[e] : 0u;
         }
     }
 }
@@ -205,13 +284,26 @@ __device__ void warp_segment(const float* __restrict__ img, const LT* __restrict
     for (int x = lane; x < tst; x += 32) tile[x] = 0u;
     int s0 = 1;                                          // slot of the group's first row; row y lives in slot (y+1) mod (R+1)
 
+    // the map's plane pointers as opaque register pairs: every staging load is then one wide multiply-add away instead of
+    // being re-derived from the kernel arguments
+    const float* imgv = img;
+    const LT* labv = lab;
+    if (VEC) { asm volatile("" : "+l"(imgv)); asm volatile("" : "+l"(labv)); }
+
+    if (VEC) raw_request<LT>(imgv, labv, (uint32_t)HW, (uint32_t)(bb.y * W + x0a), W, nq, rnq, min(R, h), full, sm.raw, lane);
+
     for (int yb = 0; yb < h; yb += R) {
         __syncwarp();                                    // the previous group's walks are done with the slots about to be rewritten
         const int nr = min(R, h - yb);
         if (VEC) {
             const uint32_t base = (uint32_t)((bb.y + yb) * W + x0a);
-            if (full) stage_rows_vec<LT, true>(img, lab, (uint32_t)HW, base, W, key, w, dx, nq, rnq, nr, s0, R, tst, tile, lane);
-            else stage_rows_vec<LT, false>(img, lab, (uint32_t)HW, base, W, key, w, dx, nq, rnq, nr, s0, R, tst, tile, lane);
+            raw_convert<LT>(key, w, dx, nq, rnq, nr, s0, R, tst, full, sm.raw, tile, lane);
+            if (nr * nq > RawWindow<LT>::quads) {        // the part of a large group that does not fit the window: straight from HBM
+                if (full) stage_rows_vec<LT, true>(imgv, labv, (uint32_t)HW, base, W, key, w, dx, nq, rnq, nr, s0, R, tst, tile, lane, RawWindow<LT>::quads);
+                else stage_rows_vec<LT, false>(imgv, labv, (uint32_t)HW, base, W, key, w, dx, nq, rnq, nr, s0, R, tst, tile, lane, RawWindow<LT>::quads);
+            }
+            // the next group's quads fly while this group is walked twice
+            if (yb + R < h) raw_request<LT>(imgv, labv, (uint32_t)HW, base + (uint32_t)(R * W), W, nq, rnq, min(R, h - yb - R), full, sm.raw, lane);
         } else {
             if (full) stage_rows<LT, true>(imgp + (int64_t)yb * W, labp + (int64_t)yb * W, HW, W, key, w, rw, nr, s0, R, tst, tile, lane);
             else stage_rows<LT, false>(imgp + (int64_t)yb * W, labp + (int64_t)yb * W, HW, W, key, w, rw, nr, s0, R, tst, tile, lane);
@@ -334,7 +426,7 @@ __device__ void warp_segment(const float* __restrict__ img, const LT* __restrict
 }
 
 template <typename LT, bool VEC>
-__global__ void __launch_bounds__(EST_WARPS * 32) estimate_kernel(Tables t, Inputs in, EstParams p) {
+__global__ void __launch_bounds__(EST_WARPS * 32, 4) estimate_kernel(Tables t, Inputs in, EstParams p) {
     extern __shared__ __align__(16) unsigned char est_smem[];
     WarpSmem* wsm = reinterpret_cast<WarpSmem*>(est_smem);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;

@@ -39,7 +39,7 @@ struct Inputs {            // the caller's device buffers of the current call
 
 constexpr int BIG_CTAS = 2;       // big-segment CTAs per label map
 constexpr int CLOG2_N = 4096;
-constexpr int EST_MAX_W = 256;    // widest bbox the warp path holds in registers (32 strips of 8 pixels)
+constexpr int EST_MAX_W = 224;    // widest bbox of the warp path: a one-row group (two row slots) must fit the warp's tile
 constexpr int EST_MAX_AREA = 1 << 20;
 
 // Segments the warp path leaves to the big-segment kernel: Rule M can fire (chunk = ceil(N/65536) >= L_min,
