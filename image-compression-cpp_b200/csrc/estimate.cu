@@ -2,21 +2,24 @@
 // Replaces the reference's 13 stream operations per segment (src/png_size_estimator.cu:505-590),
 // its two nested host loops (src/compute_rewards.cu:125,159) and its RGBA staging kernel (:23-53).
 //
-// Persistent warps pull segments from the flat work list prep built.  A warp owns one segment and walks
-// its bbox in groups of R rows:
-//   stage    every lane takes pixels of the group in row-major order (coalesced, all lanes busy whatever
-//            the width): three f32 planes -> saturating round to bytes (Rule C), raw label compared with
-//            the segment's key (Rule P) -> one masked RGBA word in a shared-memory tile.  The row above
-//            the group stays in a rolling slot; a zero guard column stands left of x = 0.
+// Persistent warps pull segments from the flat work list prep built, one per request with the next request in
+// flight.  A warp owns one segment and walks its bbox in groups of R rows:
+//   stage    every lane takes pixels of the group as aligned quads in row-major order (coalesced, all lanes busy
+//            whatever the width).  The quads of group g+1 are requested with cp.async into the warp's raw window
+//            while group g is walked, so their latency is not waited for; on arrival: three f32 planes ->
+//            saturating round to bytes (Rule C), raw label compared with the segment's key (Rule P) -> one masked
+//            RGBA word in a shared-memory tile.  The row above the group stays in a rolling slot; a zero guard
+//            column stands left of x = 0.
 //   costs    lane = (row of the group, strip of the row).  It walks its strip left to right with the left
 //            and upper-left neighbours carried in registers, accumulates the five filter costs with
 //            packed-byte arithmetic and parks the Avg and Paeth predictors in two small planes.
 //   choose   strips of a row are combined by a butterfly; arg-min with ties to the lowest id (Rule F).
 //   residual second walk: predictor = one shared-memory load whose base/step depend on the row's filter
-//            (zero word, left, up, Avg plane, Paeth plane), residual bytes go to the warp's 4x256
-//            histogram.  Zero residuals are not sent; bin 0 is recovered as w*h minus the rest.
+//            (zero word, left, up, Avg plane, Paeth plane), the four residual bytes of every pixel of the bbox
+//            (zeros included) go to the warp's 4x256 histogram with unconditional ATOMS.POPC.INC.
+//   entropy  branch-free c*log2(c) table look-ups, Rule Z, one f64 store per segment.
 // No residual stream, RGBA plane or compact-id plane is ever written to global memory.  Segments that
-// need Rule M match statistics (chunk >= L_min) or are wider than 256 px go to the big-segment kernel.
+// need Rule M match statistics (chunk >= L_min) or are wider than EST_MAX_W go to the big-segment kernel.
 #include "icr_internal.h"
 #include "icr_pixel.cuh"
 
@@ -75,7 +78,7 @@ __device__ __forceinline__ int choose_geometry(int w, int h) {
     for (int l = 0; l <= 5; ++l) {
         const int sw = (w + (1 << l) - 1) >> l;
         const int groups = ((h << l) + 31) >> 5;
-        const int cost = groups * (20 * sw + 14 + 3 * l);      // per group: sw pixel steps (~70 instructions each) + set-up, butterfly, choice
+        const int cost = groups * (20 * sw + 50 + 3 * l);      // per group: sw pixel steps (~70 instructions each) + ~180 for request, conversion, butterfly, choice
         if (sw <= MAXSW && ((32 >> l) + 1) * (w + 2) <= TILE_CAP && cost < best) { best = cost; lg = l; }
     }
     return lg;
