@@ -93,12 +93,13 @@ __device__ __forceinline__ int map_of_segment(const int32_t* __restrict__ sp, in
     return lo;
 }
 
-// ---- emit (Rule C + Rule P): one CTA per segment, one warp per slice row, lanes along x; the slice row is contiguous
-// in the packed buffer, so stores are coalesced and the loads are row fragments of the three planes and the label map.
+// ---- emit (Rule C + Rule P): one CTA per segment, threads along the slice's pixels in row-major order: the slice is
+// contiguous in the packed buffer, so stores are fully coalesced and the loads are row fragments of the three planes and
+// the label map.
 template <typename LT, bool SWAP>
 __global__ void __launch_bounds__(EMIT_T) slice_emit_kernel(Tables t, Inputs in, const unsigned long long* __restrict__ offsets,
                                                              uint32_t* __restrict__ out, unsigned long long cap_px) {
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
     const int total = __ldg(t.seg_prefix + t.V);
     const int64_t HW = (int64_t)t.H * t.W;
     for (int flat = blockIdx.x; flat < total; flat += gridDim.x) {
@@ -113,15 +114,30 @@ __global__ void __launch_bounds__(EMIT_T) slice_emit_kernel(Tables t, Inputs in,
         const float* __restrict__ img = in.images + (int64_t)(v / in.S) * 3 * HW + (int64_t)bb.y * t.W + bb.x;
         const LT* __restrict__ lab = static_cast<const LT*>(in.labels) + (int64_t)v * HW + (int64_t)bb.y * t.W + bb.x;
         uint32_t* __restrict__ dst = out + o;
-        for (int y = warp; y < h; y += EMIT_T / 32) {
-            const int64_t g0 = (int64_t)y * t.W;
-            for (int x = lane; x < w; x += 32) {
-                uint32_t px = 0u;
-                if (lab[g0 + x] == key) {
-                    const float c0 = __ldg(img + g0 + x), c1 = __ldg(img + HW + g0 + x), c2 = __ldg(img + 2 * HW + g0 + x);
-                    px = SWAP ? rgba_of(c2, c1, c0) : rgba_of(c0, c1, c2);
+        // lanes take the bbox pixels in row-major order, four independent pixels per lane in flight; all four loads of a
+        // pixel are issued together (the planes are read for masked-out pixels too: one latency instead of two)
+        const int n = w * h;                                       // the warp path's and the big kernel's bboxes are below 2^31 pixels
+        const float rw = 1.0f / (float)w;
+        constexpr int U = 4;
+        for (int i0 = threadIdx.x; i0 < n; i0 += EMIT_T * U) {
+            float c0[U], c1[U], c2[U];
+            LT l[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int i = i0 + u * EMIT_T;
+                if (i < n) {
+                    int y = __float2int_rz(((float)i + 0.5f) * rw);        // i / w; corrected below where the float estimate is off by one
+                    y += (y + 1) * w <= i;
+                    y -= y * w > i;
+                    const int64_t g = (int64_t)y * t.W + (i - y * w);
+                    l[u] = lab[g];
+                    c0[u] = __ldg(img + g); c1[u] = __ldg(img + HW + g); c2[u] = __ldg(img + 2 * HW + g);
                 }
-                dst[(int64_t)y * w + x] = px;
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int i = i0 + u * EMIT_T;
+                if (i < n) dst[i] = l[u] == key ? (SWAP ? rgba_of(c2[u], c1[u], c0[u]) : rgba_of(c0[u], c1[u], c2[u])) : 0u;
             }
         }
     }

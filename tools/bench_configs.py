@@ -14,6 +14,13 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
 
+def hbm_peak():
+    try:
+        return float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"])
+    except Exception:
+        return 6552.3
+
+
 def run(name, images, labels, sizes, pool_reps, steps=10):
     import torch
     from image_compression_cpp_b200 import reward
@@ -89,7 +96,7 @@ def run(name, images, labels, sizes, pool_reps, steps=10):
             tp += ev[0].elapsed_time(ev[1]) / steps
             te += ev[1].elapsed_time(ev[2]) / steps
     print(json.dumps({"config": name + " -- slices", "segments": nseg, "slice_bytes": nbytes, "plan_ms": tp, "emit_ms": te,
-                      "emit_GBps": (nbytes * 5) / (te * 1e-3) / 1e9, "images_per_sec": B / ((tp + te) * 1e-3),
+                      "emit_GBps": (nbytes * 5) / (te * 1e-3) / 1e9, "emit_frac_of_hbm_peak": (nbytes * 5) / (te * 1e-3) / 1e9 / hbm_peak(), "images_per_sec": B / ((tp + te) * 1e-3),
                       "note": "emit traffic = 16 B read (3 f32 planes + int32 label) + 4 B written per bbox pixel"}))
     ws.close()
 
