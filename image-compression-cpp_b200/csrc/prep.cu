@@ -24,6 +24,10 @@ __device__ __forceinline__ void load_labels(const LT* lab, int64_t p, bool inran
     if constexpr (VEC == 4 && sizeof(LT) == 4) {
         int4 q = inrange ? __ldg(reinterpret_cast<const int4*>(lab + p)) : make_int4(0, 0, 0, 0);
         out[0] = q.x; out[1] = q.y; out[2] = q.z; out[3] = q.w;
+    } else if constexpr (VEC == 8 && sizeof(LT) == 4) {
+        int4 q = make_int4(0, 0, 0, 0), r = q;
+        if (inrange) { q = __ldg(reinterpret_cast<const int4*>(lab + p)); r = __ldg(reinterpret_cast<const int4*>(lab + p + 4)); }
+        out[0] = q.x; out[1] = q.y; out[2] = q.z; out[3] = q.w; out[4] = r.x; out[5] = r.y; out[6] = r.z; out[7] = r.w;
     } else if constexpr (VEC == 4 && sizeof(LT) == 8) {
         longlong2 a = make_longlong2(0, 0), b = a;
         if (inrange) { a = __ldg(reinterpret_cast<const longlong2*>(lab + p)); b = __ldg(reinterpret_cast<const longlong2*>(lab + p + 2)); }
@@ -60,8 +64,11 @@ __device__ __forceinline__ void sweep_runs(const LT* __restrict__ lab, int64_t H
 #pragma unroll
             for (int i = 0; i < VEC; ++i) id[i] = (i > 0 && l[i] == l[i - 1]) ? id[i - 1] : rank_of(l[i]);
             int32_t* co = compact_row + p;
-            if constexpr (VEC == 4) *reinterpret_cast<int4*>(co) = make_int4((int)id[0], (int)id[1], (int)id[2], (int)id[3]);
-            else co[0] = (int)id[0];
+            if constexpr (VEC >= 4) {
+#pragma unroll
+                for (int j = 0; j < VEC; j += 4)
+                    *reinterpret_cast<int4*>(co + j) = make_int4((int)id[j], (int)id[j + 1], (int)id[j + 2], (int)id[j + 3]);
+            } else co[0] = (int)id[0];
         }
         // ---- run heads among this lane's pixels: the label differs from the pixel before, or a row / the warp's span starts
         const LT prevl = __shfl_up_sync(0xffffffffu, l[VEC - 1], 1);
@@ -364,6 +371,7 @@ cudaError_t launch_prep(const void* labels, int label_dtype, const Tables& t, in
     const bool i64 = label_dtype == ICR_LABELS_I64;
     const bool vec = (t.W % 4 == 0) && ((uintptr_t)labels % 16 == 0) && HW % 4 == 0 && (!compact_out || (uintptr_t)compact_out % 16 == 0);
     if (i64) return vec ? launch_t<int64_t, 4>(labels, t, compact_out, st) : launch_t<int64_t, 1>(labels, t, compact_out, st);
+    if (vec && t.W % 8 == 0 && HW % 8 == 0 && !compact_out) return launch_t<int32_t, 8>(labels, t, compact_out, st);
     return vec ? launch_t<int32_t, 4>(labels, t, compact_out, st) : launch_t<int32_t, 1>(labels, t, compact_out, st);
 }
 
