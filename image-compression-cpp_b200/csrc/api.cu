@@ -34,7 +34,7 @@ static int cuda_fail(cudaError_t e, const char* what) {
 
 static size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
 
-struct Layout { size_t K, status, counts, bboxes, keys, sizes, err, seg_prefix, sched, big_filter, clog2, runs, slice_map_off, total; };
+struct Layout { size_t K, status, counts, bboxes, keys, sizes, err, seg_prefix, sched, big_filter, clog2, runs, slice_map_off, map_max, big_done, total; };
 
 static Layout layout(int V, int H, int W, int Kmax) {
     Layout l; size_t o = 0;
@@ -51,6 +51,8 @@ static Layout layout(int V, int H, int W, int Kmax) {
     l.clog2 = o; o = align_up(o + (size_t)CLOG2_N * 8);
     l.runs = o; o = align_up(o + (size_t)V * run_capacity(H, W) * 8);
     l.slice_map_off = o; o = align_up(o + (size_t)V * 8);
+    l.map_max = o; o = align_up(o + (size_t)V * 8);
+    l.big_done = o; o = align_up(o + (size_t)V * 4);
     l.total = o;
     return l;
 }
@@ -119,6 +121,7 @@ int icr_workspace_create(icr_workspace** out, int device, int V, int H, int W, i
     t.V = V; t.H = H; t.W = W; t.Kmax = Kmax;
     t.runs = (uint2*)(ws->base + l.runs); t.run_cap = run_capacity(H, W);
     t.slice_map_off = (unsigned long long*)(ws->base + l.slice_map_off);
+    t.map_max = (int2*)(ws->base + l.map_max); t.big_done = (int32_t*)(ws->base + l.big_done);
     std::vector<double> tab(CLOG2_N);
     tab[0] = 0.0;
     for (int c = 1; c < CLOG2_N; ++c) tab[c] = (double)c * std::log2((double)c);
@@ -128,6 +131,8 @@ int icr_workspace_create(icr_workspace** out, int device, int V, int H, int W, i
     if (e == cudaSuccess) e = cudaMemset(ws->base + l.err, 0, 16);
     if (e == cudaSuccess) e = cudaMemset(ws->base + l.seg_prefix, 0, ((size_t)V + 1) * 4);
     if (e == cudaSuccess) e = cudaMemset(ws->base + l.sched, 0, 16);
+    if (e == cudaSuccess) e = cudaMemset(ws->base + l.big_done, 0, (size_t)V * 4);
+    if (e == cudaSuccess) e = cudaMemset(ws->base + l.map_max, 0x7f, (size_t)V * 8);
     if (e != cudaSuccess) { cudaFree(ws->base); delete ws; return cuda_fail(e, "workspace init"); }
     *out = ws;
     return ICR_OK;
@@ -163,9 +168,10 @@ int icr_compute_rewards(const float* images, const void* labels, int label_dtype
     if (prof) cudaEventRecord(ws->ev[1], st);
     ICR_CUDA(launch_estimate(t, in, p, st), "estimate");
     if (prof) cudaEventRecord(ws->ev[2], st);
-    ICR_CUDA(launch_big(t, in, p, st), "big_segment");
+    bool fused = false;                                  // the big-segment kernel, when it runs, also does Rule W
+    ICR_CUDA(launch_big(t, in, p, image_sizes, rewards, &fused, st), "big_segment");
     if (prof) cudaEventRecord(ws->ev[3], st);
-    ICR_CUDA(launch_reward(t, p, image_sizes, S, rewards, st), "reward");
+    if (!fused) ICR_CUDA(launch_reward(t, p, image_sizes, S, rewards, st), "reward");
     if (prof) cudaEventRecord(ws->ev[4], st);
     return ICR_OK;
 }

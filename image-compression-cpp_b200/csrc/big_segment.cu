@@ -8,6 +8,7 @@
 // Entropy and mean follow the reference's reduction trees (:281-328) exactly.
 #include "icr_internal.h"
 #include "icr_pixel.cuh"
+#include "icr_reward.cuh"
 
 namespace icr {
 
@@ -154,28 +155,57 @@ __device__ void block_segment(const Src& src, int x0, int y0, int w, int h, int 
 
 __device__ __forceinline__ bool flagged(int4 bb, int L_min) { return for_big_kernel(bb.z - bb.x + 1, bb.w - bb.y + 1, L_min); }
 
+// Persistent CTAs walk the (label map, part) pairs.  Most maps hold no segment for this kernel: prep left the largest
+// bbox of every map, so those pairs cost two loads -- and, when Rule W is fused in (rewards != NULL), a warp computes
+// their reward up front.  Maps that do hold such segments split them over BIG_CTAS parts; the part that finishes last
+// computes the reward, every segment size of the map being final then.
 template <typename LT>
-__global__ void __launch_bounds__(BIG_T) big_kernel(Tables t, Inputs in, EstParams p) {
-    const int v = blockIdx.y;
-    if (t.status[v] != ST_OK) return;
-    const int K = t.K[v];
+__global__ void __launch_bounds__(BIG_T) big_kernel(Tables t, Inputs in, EstParams p, const double* __restrict__ image_sizes,
+                                                    double* __restrict__ rewards) {
+    __shared__ int s_last;
     const int64_t HW = (int64_t)t.H * t.W;
-    const int4* bbs = t.bboxes + (int64_t)v * t.Kmax;
-    double* sizes = t.seg_sizes + (int64_t)v * t.Kmax;
-    uint8_t* filt = t.big_filter + ((int64_t)v * BIG_CTAS + blockIdx.x) * t.H;
     BigDebug none{};
-    for (int k0 = 0; k0 < K; k0 += BIG_T) {
-        const int k = k0 + threadIdx.x;
-        const int mine = (k < K && (k % BIG_CTAS) == (int)blockIdx.x && flagged(__ldg(bbs + k), p.L_min)) ? 1 : 0;
-        if (!__syncthreads_or(mine)) continue;
-        const int kend = min(k0 + BIG_T, K);
-        for (int kk = k0 + (((int)blockIdx.x - k0) % BIG_CTAS + BIG_CTAS) % BIG_CTAS; kk < kend; kk += BIG_CTAS) {
-            const int4 bb = __ldg(bbs + kk);
-            if (!flagged(bb, p.L_min)) continue;
-            SrcPlanar<LT> src{in.images + (int64_t)(v / in.S) * 3 * HW, static_cast<const LT*>(in.labels) + (int64_t)v * HW, HW, t.W,
-                              (LT)t.keys[(int64_t)v * t.Kmax + kk]};
-            block_segment(src, bb.x, bb.y, bb.z - bb.x + 1, bb.w - bb.y + 1, 4, p, filt, sizes + kk, none);
+    // maps without such a segment: their sizes all come from the estimate kernel; a warp per map does Rule W
+    if (rewards)
+        for (int v = blockIdx.x * (BIG_T / 32) + (threadIdx.x >> 5); v < t.V; v += gridDim.x * (BIG_T / 32)) {
+            const int2 mm = t.map_max[v];
+            if (t.status[v] != ST_OK || !map_may_need_big_kernel(mm.x, mm.y, p.L_min))
+                reward_of_map<false>(t, p, image_sizes, in.S, rewards, v, threadIdx.x & 31);
         }
+    for (int pair = blockIdx.x; pair < t.V * BIG_CTAS; pair += gridDim.x) {
+        const int v = pair / BIG_CTAS, part = pair % BIG_CTAS;
+        const int2 mm = t.map_max[v];
+        if (t.status[v] != ST_OK || !map_may_need_big_kernel(mm.x, mm.y, p.L_min)) continue;
+        const int K = t.K[v];
+        const int4* bbs = t.bboxes + (int64_t)v * t.Kmax;
+        double* sizes = t.seg_sizes + (int64_t)v * t.Kmax;
+        uint8_t* filt = t.big_filter + ((int64_t)v * BIG_CTAS + part) * t.H;
+        for (int k0 = 0; k0 < K; k0 += BIG_T) {
+            const int k = k0 + threadIdx.x;
+            const int mine = (k < K && (k % BIG_CTAS) == part && flagged(__ldg(bbs + k), p.L_min)) ? 1 : 0;
+            if (!__syncthreads_or(mine)) continue;
+            const int kend = min(k0 + BIG_T, K);
+            for (int kk = k0 + ((part - k0) % BIG_CTAS + BIG_CTAS) % BIG_CTAS; kk < kend; kk += BIG_CTAS) {
+                const int4 bb = __ldg(bbs + kk);
+                if (!flagged(bb, p.L_min)) continue;
+                SrcPlanar<LT> src{in.images + (int64_t)(v / in.S) * 3 * HW, static_cast<const LT*>(in.labels) + (int64_t)v * HW, HW, t.W,
+                                  (LT)t.keys[(int64_t)v * t.Kmax + kk]};
+                block_segment(src, bb.x, bb.y, bb.z - bb.x + 1, bb.w - bb.y + 1, 4, p, filt, sizes + kk, none);
+            }
+        }
+        if (!rewards) continue;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            __threadfence();
+            s_last = atomicAdd(&t.big_done[v], 1) == BIG_CTAS - 1;
+            if (s_last) t.big_done[v] = 0;
+        }
+        __syncthreads();
+        if (s_last && threadIdx.x < 32) {
+            __threadfence();
+            reward_of_map<true>(t, p, image_sizes, in.S, rewards, v, threadIdx.x);
+        }
+        __syncthreads();                                   // s_last is reused by the next pair
     }
 }
 
@@ -195,11 +225,15 @@ __global__ void __launch_bounds__(BIG_T) single_segment_kernel(SrcRaw src, int x
     block_segment(src, x0, y0, w, h, src.C, p, filt, out, dbg);
 }
 
-cudaError_t launch_big(const Tables& t, const Inputs& in, const EstParams& p, cudaStream_t st) {
+cudaError_t launch_big(const Tables& t, const Inputs& in, const EstParams& p, const double* image_sizes, double* rewards,
+                       bool* launched, cudaStream_t st) {
     // no segment of an HxW map can need this kernel unless the whole map would
+    if (launched) *launched = false;
     if (!for_big_kernel(t.W, t.H, p.L_min)) return cudaSuccess;
-    if (in.label_dtype == ICR_LABELS_I64) big_kernel<int64_t><<<dim3(BIG_CTAS, t.V), BIG_T, 0, st>>>(t, in, p);
-    else big_kernel<int32_t><<<dim3(BIG_CTAS, t.V), BIG_T, 0, st>>>(t, in, p);
+    if (launched) *launched = true;
+    const int grid = min(t.V * BIG_CTAS, 148 * 2);
+    if (in.label_dtype == ICR_LABELS_I64) big_kernel<int64_t><<<grid, BIG_T, 0, st>>>(t, in, p, image_sizes, rewards);
+    else big_kernel<int32_t><<<grid, BIG_T, 0, st>>>(t, in, p, image_sizes, rewards);
     count_launch();
     return cudaGetLastError();
 }

@@ -25,6 +25,8 @@ struct Tables {            // device pointers into the workspace, V label maps
     uint8_t* big_filter;   // [V*BIG_CTAS, H] filter ids of the segment a big-kernel CTA is working on
     uint2* runs;           // [V, run_cap] label runs of a map found by prep's first sweep {slot | (len-1)<<20, y<<16 | x}
     int run_cap;           // 0 = no run list (very wide maps)
+    int2* map_max;         // [V] {largest bbox area, widest bbox} of a map (INT_MAX when not known): lets the big-segment kernel skip maps
+    int32_t* big_done;     // [V] big-segment CTAs of a map that have finished (self-resetting)
     unsigned long long* slice_map_off;   // [V] byte offset of a map's first slice in the packed slice buffer (slices.cu)
     const double* clog2;   // [CLOG2_N] c*log2(c)
     int V, H, W, Kmax;
@@ -50,6 +52,11 @@ __host__ __device__ inline bool for_big_kernel(int w, int h, int L_min) {
     return (N + 65535) / 65536 >= (long long)L_min || w > EST_MAX_W || (long long)w * h > EST_MAX_AREA;
 }
 
+// can a map whose largest bbox has `area` pixels and whose widest bbox has `maxw` columns hold a big-kernel segment?
+__host__ __device__ inline bool map_may_need_big_kernel(int area, int maxw, int L_min) {
+    return (4ll * area + 65535) / 65536 >= (long long)L_min || maxw > EST_MAX_W || (long long)area > EST_MAX_AREA;
+}
+
 struct EstParams {         // icr_params widened the way the reference does (:588)
     int32_t min_pixels, L_min, adaptive;
     double beta, token, gamma, overhead, lambda;
@@ -73,7 +80,10 @@ inline int run_capacity(int H, int W) {
 // launchers (each returns the cudaError_t of its launches)
 cudaError_t launch_prep(const void* labels, int label_dtype, const Tables& t, int32_t* compact_out, cudaStream_t st);
 cudaError_t launch_estimate(const Tables& t, const Inputs& in, const EstParams& p, cudaStream_t st);
-cudaError_t launch_big(const Tables& t, const Inputs& in, const EstParams& p, cudaStream_t st);
+// image_sizes/rewards non-null: the last big-segment CTA of each map also computes the map's reward (Rule W), so the
+// reward kernel is not launched; *launched tells whether the kernel ran at all
+cudaError_t launch_big(const Tables& t, const Inputs& in, const EstParams& p, const double* image_sizes, double* rewards,
+                       bool* launched, cudaStream_t st);
 cudaError_t launch_reward(const Tables& t, const EstParams& p, const double* image_sizes, int S,
                           double* rewards, cudaStream_t st);
 cudaError_t launch_estimate_debug(const Tables& t, const Inputs& in, const EstParams& p, int v, int k, uint32_t* row_costs,

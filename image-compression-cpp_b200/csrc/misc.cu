@@ -2,6 +2,7 @@
 // the compact-label stats drop-in (Rule S), EMA baseline + advantage (Rule E) and the self-test.
 #include "icr_internal.h"
 #include "icr_pixel.cuh"
+#include "icr_reward.cuh"
 
 namespace icr {
 
@@ -10,20 +11,7 @@ __global__ void __launch_bounds__(128) reward_kernel(Tables t, EstParams p, cons
                                                       int S, double* __restrict__ rewards) {
     const int v = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (v >= t.V) return;
-    if (t.status[v] != ST_OK) { if (lane == 0) rewards[v] = __longlong_as_double(0x7ff8000000000000ll); return; }
-    const int K = t.K[v];
-    const double* sz = t.seg_sizes + (int64_t)v * t.Kmax;
-    const int32_t* cnt = t.counts + (int64_t)v * t.Kmax;
-    double sum = 0.0;
-    int valid = 0;
-    for (int k = lane; k < K; k += 32) { sum += sz[k]; valid += cnt[k] >= p.min_pixels ? 1 : 0; }
-    for (int o = 16; o; o >>= 1) { sum += __shfl_xor_sync(0xffffffffu, sum, o); valid += __shfl_xor_sync(0xffffffffu, valid, o); }
-    if (lane == 0) {
-        if (K <= 0) { rewards[v] = 0.0; return; }                   // :136-139
-        const double s_img = image_sizes[v / S];
-        const double P = valid == 1 ? 1.0 : 0.0;
-        rewards[v] = (s_img - sum) / s_img - p.lambda * P;
-    }
+    reward_of_map<false>(t, p, image_sizes, S, rewards, v, lane);
 }
 
 cudaError_t launch_reward(const Tables& t, const EstParams& p, const double* image_sizes, int S, double* rewards, cudaStream_t st) {

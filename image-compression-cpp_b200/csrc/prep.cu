@@ -204,7 +204,7 @@ __global__ void __launch_bounds__(PREP_T, 2) prep_kernel(const LT* __restrict__ 
     __shared__ long long red_lo[PREP_T / 32], red_hi[PREP_T / 32];
     __shared__ uint32_t warp_tot[PREP_T / 32];
     __shared__ long long s_min;
-    __shared__ int s_bad, s_last, s_nruns;
+    __shared__ int s_bad, s_last, s_nruns, s_maxarea, s_maxw;
 
     const int v = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int H = t.H, W = t.W;
@@ -215,7 +215,7 @@ __global__ void __launch_bounds__(PREP_T, 2) prep_kernel(const LT* __restrict__ 
     int bad = ST_OK;
 
     for (int i = tid; i < cap_words; i += PREP_T) bitmap[i] = 0;
-    if (tid == 0) s_nruns = 0;
+    if (tid == 0) { s_nruns = 0; s_maxarea = 0; s_maxw = 0; }
     __syncthreads();
     // the run list serves the batch path; the compact-id output needs a pixel pass anyway
     const bool use_list = !COMPACT_OUT && t.run_cap > 0;
@@ -309,10 +309,16 @@ __global__ void __launch_bounds__(PREP_T, 2) prep_kernel(const LT* __restrict__ 
             if (use_list && s_nruns <= t.run_cap) sweep_list<true>(runs, s_nruns, st, rank_slot);
             else sweep_runs<LT, VEC, true, COMPACT_OUT>(lab, HW, W, st, rank_of, compact_row);
             __syncthreads();
+            int marea = 0, mw = 0;
             for (int k = tid; k < K; k += PREP_T) {
                 g_cnt[k] = st.cnt[k];
                 t.bboxes[(int64_t)v * t.Kmax + k] = make_int4(st.bx0[k], st.by0[k], st.bx1[k], st.by1[k]);
+                const int bw = st.bx1[k] - st.bx0[k] + 1, bh = st.by1[k] - st.by0[k] + 1;
+                marea = max(marea, bw * bh); mw = max(mw, bw);
             }
+            marea = __reduce_max_sync(0xffffffffu, marea); mw = __reduce_max_sync(0xffffffffu, mw);
+            if (lane == 0 && marea > 0) { atomicMax(&s_maxarea, marea); atomicMax(&s_maxw, mw); }
+            __syncthreads();
         } else {
             const StatsPtr st{g_cnt, g_bb, g_bb + 1, g_bb + 2, g_bb + 3, 4};
             for (int k = tid; k < K; k += PREP_T) { g_cnt[k] = 0; g_bb[4 * k] = W; g_bb[4 * k + 1] = H; g_bb[4 * k + 2] = -1; g_bb[4 * k + 3] = -1; }
@@ -325,6 +331,8 @@ __global__ void __launch_bounds__(PREP_T, 2) prep_kernel(const LT* __restrict__ 
     // ---- publish, and let the last CTA build the flat work list (exclusive scan of the usable segment counts)
     if (tid == 0) {
         t.K[v] = bad == ST_LABEL_RANGE ? 0 : K;
+        // the largest bbox of the map, for the big-segment kernel's early exit; not tracked when the rows live in global memory
+        t.map_max[v] = (bad || K > KS_SMEM) ? make_int2(INT_MAX, INT_MAX) : make_int2(s_maxarea, s_maxw);
         t.status[v] = bad;
         if (bad) { atomicExch(&t.err[0], 1); atomicMax(&t.err[1], 0x7fffffff - v); }
         __threadfence();
