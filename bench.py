@@ -283,6 +283,18 @@ def main():
     e2e_ms = max_over_ranks(e0.elapsed_time(e1))
     e2e_value = B * world * e2e_steps / (e2e_ms * 1e-3)
     assert np.array_equal(pr.numpy(), rewards.cpu().numpy()), "host-buffer entry and device entry disagree"
+    # what the link alone takes for the same pinned buffers: e2e cannot go below this
+    scratch_i, scratch_l = torch.empty_like(ti), torch.empty_like(tl)
+    for _ in range(2):
+        scratch_i.copy_(pi, non_blocking=True); scratch_l.copy_(pl, non_blocking=True)
+    sync()
+    e0.record()
+    for _ in range(5):
+        scratch_i.copy_(pi, non_blocking=True); scratch_l.copy_(pl, non_blocking=True)
+    e1.record()
+    sync()
+    copy_ms = max_over_ranks(e0.elapsed_time(e1)) / 5
+    del scratch_i, scratch_l
 
     # ---- roofline of the dominant kernel: per-kernel device times from events between the launches
     L.icr_workspace_set_profile(ws.handle, 1)
@@ -315,7 +327,9 @@ def main():
                    "parallelism": f"dp{world}: images sharded, one NCCL all-gather of the rewards per step, EMA on the gathered vector" if world > 1 else "single GPU"},
         "e2e": {"value": e2e_value, "unit": "images/sec", "h2d_bytes_per_step": int(images.nbytes + labels.nbytes + sizes.nbytes),
                 "d2h_bytes_per_step": int(pr.numel() * 8), "ms_per_step": e2e_ms / e2e_steps, "steps": e2e_steps,
-                "api": "icr_compute_rewards_host (C ABI, pinned host buffers)"},
+                "h2d_copy_alone_ms": copy_ms,
+                "api": "icr_compute_rewards_host (C ABI, pinned host buffers; the batch is copied in four pieces on a second stream "
+                       "under the kernels of the piece before)"},
         "gpu_launches": launches,
         "roofline": {"bound": "hbm", "kernel": names[top], "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": traffic, "traffic_source": "profiles/r01_traffic.json (ncu --set full, per launch)" if traffic else None,

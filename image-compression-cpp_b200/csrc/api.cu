@@ -7,6 +7,8 @@
 #include <string>
 #include <vector>
 
+constexpr int HOST_CHUNKS = 4;     // pieces the host-buffer entry cuts a batch into
+
 struct icr_workspace {
     int device, V, H, W, Kmax;
     char* base;            // one device allocation
@@ -16,6 +18,8 @@ struct icr_workspace {
     // device staging for the host-buffer entry
     float* st_images; void* st_labels; double* st_sizes; double* st_rewards;
     size_t st_images_bytes, st_labels_bytes;
+    cudaStream_t copy_stream;      // the host-buffer entry copies the next chunk on it while the current one is computed
+    cudaEvent_t copy_ev[HOST_CHUNKS + 1];
     int profile;           // record events between the kernels of icr_compute_rewards
     cudaEvent_t ev[5];
 };
@@ -144,6 +148,10 @@ int icr_workspace_destroy(icr_workspace* ws) {
     cudaFree(ws->base);
     cudaFree(ws->st_images); cudaFree(ws->st_labels); cudaFree(ws->st_sizes); cudaFree(ws->st_rewards);
     if (ws->ev[0]) for (int i = 0; i < 5; ++i) cudaEventDestroy(ws->ev[i]);
+    if (ws->copy_stream) {
+        for (int i = 0; i <= HOST_CHUNKS; ++i) cudaEventDestroy(ws->copy_ev[i]);
+        cudaStreamDestroy(ws->copy_stream);
+    }
     delete ws;
     return ICR_OK;
 }
@@ -200,11 +208,34 @@ int icr_compute_rewards_host(const float* images_h, const void* labels_h, int la
         ICR_CUDA(cudaMalloc((void**)&ws->st_sizes, (size_t)ws->V * 8), "cudaMalloc(staging sizes)");
         ICR_CUDA(cudaMalloc((void**)&ws->st_rewards, (size_t)ws->V * 8), "cudaMalloc(staging rewards)");
     }
-    ICR_CUDA(cudaMemcpyAsync(ws->st_images, images_h, ib, cudaMemcpyHostToDevice, st), "H2D images");
-    ICR_CUDA(cudaMemcpyAsync(ws->st_labels, labels_h, lb, cudaMemcpyHostToDevice, st), "H2D labels");
+    if (!ws->copy_stream) {
+        ICR_CUDA(cudaStreamCreateWithFlags(&ws->copy_stream, cudaStreamNonBlocking), "cudaStreamCreate(copy)");
+        for (int i = 0; i <= HOST_CHUNKS; ++i) ICR_CUDA(cudaEventCreateWithFlags(&ws->copy_ev[i], cudaEventDisableTiming), "cudaEventCreate(copy)");
+    }
+    // The batch goes over in HOST_CHUNKS pieces: the copy of piece c+1 runs on a second stream under the kernels of piece
+    // c, so the call costs the transfer plus the kernels of the last piece only.  The copies start after whatever the
+    // caller's stream still has queued (an earlier call may be reading the staging buffers).
+    const int nchunk = B >= 16 * HOST_CHUNKS ? HOST_CHUNKS : 1;
+    const size_t lsz = label_dtype == ICR_LABELS_I64 ? 8 : 4;
+    ICR_CUDA(cudaEventRecord(ws->copy_ev[HOST_CHUNKS], st), "event record");
+    ICR_CUDA(cudaStreamWaitEvent(ws->copy_stream, ws->copy_ev[HOST_CHUNKS], 0), "stream wait");
     ICR_CUDA(cudaMemcpyAsync(ws->st_sizes, image_sizes_h, (size_t)B * 8, cudaMemcpyHostToDevice, st), "H2D sizes");
-    if (int rc = icr_compute_rewards(ws->st_images, ws->st_labels, label_dtype, ws->st_sizes, B, S, H, W, params,
-                                     ws->st_rewards, ws, stream)) return rc;
+    int b0[HOST_CHUNKS + 1];
+    for (int c = 0; c <= nchunk; ++c) b0[c] = (int)((long long)B * c / nchunk);
+    for (int c = 0; c < nchunk; ++c) {
+        const size_t io = (size_t)b0[c] * 3 * HW, lo = (size_t)b0[c] * S * HW, n = (size_t)(b0[c + 1] - b0[c]);
+        ICR_CUDA(cudaMemcpyAsync(ws->st_images + io, images_h + io, n * 3 * HW * 4, cudaMemcpyHostToDevice, ws->copy_stream), "H2D images");
+        ICR_CUDA(cudaMemcpyAsync((char*)ws->st_labels + lo * lsz, (const char*)labels_h + lo * lsz, n * S * HW * lsz, cudaMemcpyHostToDevice,
+                                 ws->copy_stream), "H2D labels");
+        ICR_CUDA(cudaEventRecord(ws->copy_ev[c], ws->copy_stream), "event record");
+    }
+    for (int c = 0; c < nchunk; ++c) {
+        ICR_CUDA(cudaStreamWaitEvent(st, ws->copy_ev[c], 0), "stream wait");
+        if (int rc = icr_compute_rewards(ws->st_images + (size_t)b0[c] * 3 * HW, (const char*)ws->st_labels + (size_t)b0[c] * S * HW * lsz,
+                                         label_dtype, ws->st_sizes + b0[c], b0[c + 1] - b0[c], S, H, W, params,
+                                         ws->st_rewards + (size_t)b0[c] * S, ws, stream)) return rc;
+    }
+    if (nchunk > 1) ws->in = Inputs{nullptr, nullptr, 0, 1};      // the tables describe the last piece only: no debug/slice entry after this call
     ICR_CUDA(cudaMemcpyAsync(rewards_h, ws->st_rewards, (size_t)B * S * 8, cudaMemcpyDeviceToHost, st), "D2H rewards");
     ICR_CUDA(cudaStreamSynchronize(st), "stream sync");
     return ICR_OK;

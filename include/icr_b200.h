@@ -70,7 +70,10 @@ int icr_compute_rewards(const float* images, const void* labels, int label_dtype
                         icr_workspace* ws, icr_stream stream);
 
 /* Same through HOST buffers (pinned or pageable): H2D of images/labels/sizes, the path, D2H of
- * rewards, then a stream synchronise.  This is the call bench.py times as `e2e`. */
+ * rewards, then a stream synchronise.  This is the call bench.py times as `e2e`.  Batches of 64 images
+ * and more go over in four pieces, each copied on a second stream while the piece before it is
+ * computed; the workspace tables then describe the last piece only, so the debug/slice entries refuse
+ * to run after this call. */
 int icr_compute_rewards_host(const float* images_h, const void* labels_h, int label_dtype,
                              const double* image_sizes_h, int B, int S, int H, int W,
                              const icr_params* params, double* rewards_h,

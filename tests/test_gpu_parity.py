@@ -253,3 +253,39 @@ def test_full_size_config5_shard_properties(icr, orc, dev):
     assert np.array_equal(got[:64], got[64:128]) and np.array_equal(got[:64], got[-64:])        # deterministic across the batch
     want = orc.compute_rewards(images[:8], labels[:8], sizes[:8])
     assert _rel(got[:8], want) < RTOL
+
+
+@pytest.mark.parametrize("B,S", [(5, 1), (70, 1), (33, 2)])
+def test_host_buffer_entry_matches_device_entry(icr, orc, dev, B, S):
+    """icr_compute_rewards_host (what bench.py times as e2e): pageable host buffers in, rewards out; batches of 64 and more
+    go over in four overlapped pieces with uneven sizes, and the result must not depend on that."""
+    import ctypes as C
+    H, W = 48, 64
+    if S == 1:
+        images, labels, sizes = synth.make_batch(2, B=min(B, 8))
+        images, labels = images[:, :, :H, :W].copy(), labels[:, :H, :W].copy()
+    else:
+        images, labels, sizes = synth.make_multi_batch(B=8, S=S, H=H, W=W)
+    reps = -(-B // images.shape[0])
+    images = np.ascontiguousarray(np.tile(images, (reps, 1, 1, 1))[:B])
+    labels = np.ascontiguousarray(np.tile(labels, (reps,) + (1,) * (labels.ndim - 1))[:B])
+    sizes = np.ascontiguousarray(np.tile(sizes, reps)[:B])
+    ws = icr.Workspace(dev, B * S, H, W, None)
+    out = np.zeros(B * S, np.float64)
+    prm = icr.make_params()
+    L = icr.lib()
+    p = lambda a: a.ctypes.data_as(C.c_void_p)
+    with torch.cuda.device(dev):
+        rc = L.icr_compute_rewards_host(p(images), p(labels), int(labels.dtype == np.int64), p(sizes), B, S, H, W, C.byref(prm), p(out),
+                                        ws.handle, C.c_void_p(torch.cuda.current_stream().cuda_stream))
+    assert rc == 0, L.icr_last_error()
+    ws.check()
+    ti, tl, ts = _to(dev, images, labels, sizes)
+    want = icr.compute_rewards_batched(ti, tl, ts).cpu().numpy().reshape(-1)
+    assert np.array_equal(out, want)
+    n = min(B, 8)
+    ref = orc.compute_rewards(np.repeat(images[:n], S, axis=0), labels[:n].reshape(n * S, H, W), np.repeat(sizes[:n], S))
+    assert _rel(out[:n * S], ref) < RTOL
+    if B >= 64:            # the tables hold the last piece only: the slice entries say so instead of returning part of the batch
+        with pytest.raises(RuntimeError, match="no batch call"):
+            ws.slices()
