@@ -1,17 +1,19 @@
-// prep: one CTA per label map, labels only.  Two reference steps in two sweeps over the label plane:
+// prep: one CTA per label map, labels only.  Two reference steps in ONE sweep over the label plane:
 //   Rule L  label compaction (sorted-unique rank)   (src/compute_rewards.cu:131-141, at::_unique)
 //   Rule S  per-segment count + inclusive bbox      (src/segment_stats.cu:11-42)
 // Rule L is a circular presence bitmap in shared memory indexed by (label mod capacity): while the
-// spread max-min is below the capacity the residues are distinct, so sweep 1 sets bits and finds
+// spread max-min is below the capacity the residues are distinct, so the sweep sets bits and finds
 // min/max at once; a popcount prefix scan then gives rank = number of set bits walking up from the
 // minimum's slot.  No sort, no host sync on K.
-// Sweep 2 works on RUNS, not pixels: a warp looks at 32*VEC consecutive pixels, marks the pixels where
-// the label changes (or a row / the warp's span starts), and only those run heads rank their label
-// and update the shared-memory stats table: one add for the count and four min/max for the bbox per
-// run, all unconditional shared-memory atomics issued for every head of the span at once.  The image
-// is not touched here: the estimator masks by comparing raw labels with the segment's key.
-// The last CTA to finish also scans the per-map segment counts into the flat work list the
-// estimator's dynamic scheduler walks.
+// The sweep works on RUNS, not pixels: a warp looks at 32*VEC consecutive pixels (VEC = 8 labels per
+// lane on the int32 path), marks the pixels where the label changes (or a row / the warp's span starts),
+// and only those run heads touch the bitmap and append a record to the map's run list (sweep_mark).
+// Rule S then walks the run list (sweep_list): one add for the count and four min/max for the bbox per
+// run, unconditional shared-memory atomics.  Maps whose runs overflow the list, very wide maps and the
+// compact-id output take a second pixel sweep instead (sweep_runs).  The image is not touched here: the
+// estimator masks by comparing raw labels with the segment's key.
+// Every CTA leaves the largest bbox of its map for the big-segment kernel's early exit; the last CTA to
+// finish scans the per-map segment counts into the flat work list the estimator's scheduler walks.
 #include "icr_internal.h"
 #include <climits>
 
@@ -40,7 +42,7 @@ __device__ __forceinline__ void load_labels(const LT* lab, int64_t p, bool inran
 // shared-memory stats table of one map (or its rows in global memory when K > KS_SMEM): struct of arrays, element stride bst
 struct StatsPtr { int32_t *cnt, *bx0, *by0, *bx1, *by1; int bst; };
 
-// ---- sweep 2 on runs.  SMEM selects shared-memory atomics at compile time (a generic pointer would cost an address-space
+// ---- the second pixel sweep (fallback and compact-id output), on runs.  SMEM selects shared-memory atomics at compile time (a generic pointer would cost an address-space
 // check per atomic).
 template <typename LT, int VEC, bool SMEM, bool COMPACT_OUT, class RankOf>
 __device__ __forceinline__ void sweep_runs(const LT* __restrict__ lab, int64_t HW, int W, const StatsPtr& st, RankOf rank_of,
