@@ -289,3 +289,17 @@ def test_host_buffer_entry_matches_device_entry(icr, orc, dev, B, S):
     if B >= 64:            # the tables hold the last piece only: the slice entries say so instead of returning part of the batch
         with pytest.raises(RuntimeError, match="no batch call"):
             ws.slices()
+
+
+@pytest.mark.parametrize("H,W", [(1, 1), (1, 17), (17, 1), (3, 4), (4, 4), (2, 8), (8, 16), (5, 1000), (300, 4), (33, 36)])
+def test_degenerate_shapes(icr, orc, dev, H, W):
+    """One-pixel maps, single rows and columns, maps narrower than a quad and wider than a strip walk: every shape the
+    reference accepts.  Label layouts: one segment, one segment per pixel, vertical and horizontal stripes."""
+    rng = np.random.default_rng(H * 1000 + W)
+    images = (rng.random((4, 3, H, W), dtype=np.float32) * 255.0).astype(np.float32)
+    yy, xx = np.mgrid[0:H, 0:W]
+    labels = np.stack([np.zeros((H, W), np.int64), (yy * W + xx).astype(np.int64), (xx // 3).astype(np.int64) * 5 - 7,
+                       (yy // 2).astype(np.int64) + 100]).astype(np.int32)
+    sizes = np.full(4, 64.0 + H * W)
+    _check_batch(icr, orc, dev, images, labels, sizes, n_debug=4)
+    _check_batch(icr, orc, dev, images, labels.astype(np.int64), sizes, tables=False)

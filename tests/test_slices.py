@@ -148,3 +148,17 @@ def test_slice_entries_report_misuse(icr, dev):
     assert b"no batch call" in L.icr_last_error()
     assert L.icr_slices_emit(ws.handle, C.c_void_p(off.data_ptr()), C.c_void_p(off.data_ptr()), C.c_size_t(64), 7, None) == 1
     assert b"order" in L.icr_last_error()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("H,W", [(1, 1), (7, 30), (19, 1), (40, 52)])
+def test_slices_of_odd_shapes(icr, orc, dev, H, W):
+    rng = np.random.default_rng(H * 100 + W)
+    images = (rng.random((3, 3, H, W), dtype=np.float32) * 255.0).astype(np.float32)
+    yy, xx = np.mgrid[0:H, 0:W]
+    labels = np.stack([np.zeros((H, W), np.int64), (yy * W + xx) % 7, (xx // 4) + 3 * (yy // 5)]).astype(np.int32)
+    ws = _batch(icr, dev, images, labels, np.full(3, 500.0), prepare_only=True)
+    buf, off = _compare_with_slicer(icr, orc, ws, images, labels)
+    tb, to = torch.from_numpy(buf).to(dev), torch.from_numpy(off).to(dev)
+    for v in range(3):
+        assert np.array_equal(ws.reassemble_map(v, tb, to).cpu().numpy(), orc.chw3_f32_to_rgba(images[v]))
