@@ -106,8 +106,8 @@ int icr_workspace_create(icr_workspace** out, int device, int V, int H, int W, i
     if (!out) return fail(ICR_EINVAL, "null workspace out-pointer");
     *out = nullptr;
     if (V <= 0 || H <= 0 || W <= 0 || Kmax <= 0) return fail(ICR_EINVAL, "V, H, W and Kmax must be positive");
-    if ((int64_t)H * W > LCAP_MAX)
-        return fail(ICR_ECAPACITY, "label maps above " + std::to_string(LCAP_MAX) + " pixels are not supported yet (shared-memory bitmap)");
+    if ((int64_t)H * W >= (1ll << 31))
+        return fail(ICR_ECAPACITY, "label maps of 2^31 pixels and more are not supported (32-bit pixel offsets inside a map)");
     if ((int64_t)Kmax > (int64_t)H * W) Kmax = H * W;
     ICR_CUDA(cudaSetDevice(device), "cudaSetDevice");
     icr_workspace* ws = new icr_workspace();

@@ -62,11 +62,13 @@ struct EstParams {         // icr_params widened the way the reference does (:58
     double beta, token, gamma, overhead, lambda;
 };
 
-// label capacity (bits of the circular presence bitmap) for an HxW map: a power of two >= max(H*W, 65536)
+// label capacity (bits of the circular presence bitmap) for an HxW map: a power of two >= max(H*W, 65536), at most
+// LCAP_MAX (what shared memory holds).  Maps above LCAP_MAX pixels therefore work as long as their labels spread over
+// less than LCAP_MAX values; beyond that the map is reported (ST_LABEL_RANGE) and the host layer ranks the labels first.
 inline int64_t label_capacity(int H, int W) {
     int64_t hw = (int64_t)H * W;
     int64_t cap = 65536;
-    while (cap < hw) cap <<= 1;
+    while (cap < hw && cap < LCAP_MAX) cap <<= 1;
     return cap;
 }
 

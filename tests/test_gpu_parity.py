@@ -303,3 +303,19 @@ def test_degenerate_shapes(icr, orc, dev, H, W):
     sizes = np.full(4, 64.0 + H * W)
     _check_batch(icr, orc, dev, images, labels, sizes, n_debug=4)
     _check_batch(icr, orc, dev, images, labels.astype(np.int64), sizes, tables=False)
+
+
+def test_map_larger_than_the_label_bitmap(icr, orc, dev):
+    """A 1024x768 map (786 432 pixels) is larger than the 2^19-bit presence bitmap shared memory holds: it works as long as
+    the labels spread over fewer values than that, which any partition with fewer than 2^19 segments can be brought to."""
+    H, W = 768, 1024
+    images = np.stack([synth.image_f32_chw(1, H, W, 77)])
+    labels = synth.voronoi_partition(H, W, cell=56, jitter=20, seed=9).astype(np.int32)[None] * 3 + 11
+    got, ws = _check_batch(icr, orc, dev, images, labels, np.array([400000.0]), n_debug=3)
+    assert icr.lib().icr_label_capacity(H, W) == 1 << 19
+    # labels spread beyond the bitmap are reported, not mis-ranked
+    wide = labels.astype(np.int64)
+    wide[0, -1, -1] += 1 << 20
+    ti, tl, ts = _to(dev, images, wide, np.array([400000.0]))
+    with pytest.raises(RuntimeError, match="label spread"):
+        icr.compute_rewards_batched(ti, tl, ts, workspace=ws)
