@@ -199,7 +199,7 @@ def main():
 
     import torch
     import torch.distributed as dist
-    from image_compression_cpp_b200 import reward
+    from image_compression_cpp_b200 import reward, sharding
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -222,12 +222,40 @@ def main():
     ema = reward.EMABaseline()
     stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
 
+    # N > 1: the path's only exchange is that every rank receives all per-image rewards: one NCCL all-gather per step.
+    # ICR_BENCH_EXCHANGE=peer selects the fused variant instead (the reward kernel stores every reward straight into all
+    # ranks' gathered vectors through peer memory and a step needs one device-side barrier); measured equal at N=2
+    # (0.2945 ms per step both ways: the all-gather already runs under the next step's first kernel), so the plain
+    # collective stays the default.
+    peer = None
+    if world > 1 and os.environ.get("ICR_BENCH_EXCHANGE", "nccl") == "peer":
+        ok = torch.ones(1, device=dev)
+        try:
+            peer = sharding.PeerGather(B, dev)
+        except Exception as e:                      # noqa: BLE001 -- any failure means "not available here"
+            print(f"[bench] rank {rank}: peer gather unavailable ({type(e).__name__}: {e}); using the NCCL all-gather", file=sys.stderr)
+            ok.zero_()
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        if ok.item() == 0:
+            peer = None
+    exchange = "none" if world == 1 else ("peer stores over NVLink + flags (no collective)" if peer else "NCCL all-gather")
+    if world > 1 and os.environ.get("ICR_BENCH_EXCHANGE") == "none":
+        exchange = "NOTHING (diagnostic run, not a valid bench line)"
+
     def step():
-        rc = L.icr_compute_rewards(C.c_void_p(ti.data_ptr()), C.c_void_p(tl.data_ptr()), 0, C.c_void_p(ts.data_ptr()), B, 1, H, W,
-                                   C.byref(prm), C.c_void_p(rewards.data_ptr()), ws.handle, stream)
+        if peer is not None:
+            tg, fl, stp = peer.begin()
+            rc = L.icr_compute_rewards_gather(C.c_void_p(ti.data_ptr()), C.c_void_p(tl.data_ptr()), 0, C.c_void_p(ts.data_ptr()), B, 1, H, W,
+                                              C.byref(prm), C.c_void_p(rewards.data_ptr()), C.c_void_p(tg.data_ptr()),
+                                              C.c_void_p(fl.data_ptr()), C.c_ulonglong(stp), world, rank, ws.handle, stream)
+        else:
+            rc = L.icr_compute_rewards(C.c_void_p(ti.data_ptr()), C.c_void_p(tl.data_ptr()), 0, C.c_void_p(ts.data_ptr()), B, 1, H, W,
+                                       C.byref(prm), C.c_void_p(rewards.data_ptr()), ws.handle, stream)
         if rc:
             raise RuntimeError(L.icr_last_error().decode())
-        if world > 1:      # the only exchange on the path: every rank receives all per-image rewards, Rule E runs on them
+        if peer is not None:
+            reward.ema_update_gathered(ema, peer)
+        elif world > 1 and os.environ.get("ICR_BENCH_EXCHANGE") != "none":      # "none": diagnosis only, prints an invalid line
             dist.all_gather_into_tensor(gathered, rewards)
             ema.update(gathered)
         else:
@@ -324,7 +352,7 @@ def main():
         "data": "synthetic",
         "config": {"workload": "cfg5 shard: 512 x 224x224 RGB f32 planes per GPU, BSP-rectangle int32 label maps (labels 7*id+3)",
                    "per_gpu_batch": B, "global_batch": B * world, "mean_segments_per_image": Kmean, "l2": "inputs (411 MB/step/GPU) exceed L2; no flush",
-                   "parallelism": f"dp{world}: images sharded, one NCCL all-gather of the rewards per step, EMA on the gathered vector" if world > 1 else "single GPU"},
+                   "parallelism": f"dp{world}: images sharded, rewards exchanged by {exchange}, EMA on the gathered vector" if world > 1 else "single GPU"},
         "e2e": {"value": e2e_value, "unit": "images/sec", "h2d_bytes_per_step": int(images.nbytes + labels.nbytes + sizes.nbytes),
                 "d2h_bytes_per_step": int(pr.numel() * 8), "ms_per_step": e2e_ms / e2e_steps, "steps": e2e_steps,
                 "h2d_copy_alone_ms": copy_ms,

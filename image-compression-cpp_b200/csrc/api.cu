@@ -156,16 +156,19 @@ int icr_workspace_destroy(icr_workspace* ws) {
     return ICR_OK;
 }
 
-int icr_compute_rewards(const float* images, const void* labels, int label_dtype, const double* image_sizes,
-                        int B, int S, int H, int W, const icr_params* params, double* rewards,
-                        icr_workspace* ws, icr_stream stream) {
-    if (!images || !labels || !image_sizes || !rewards || !params) return fail(ICR_EINVAL, "null ptr");
+static int compute_rewards_impl(const float* images, const void* labels, int label_dtype, const double* image_sizes, int B, int S,
+                                int H, int W, const icr_params* params, double* rewards, double* const* peer_rewards, int peer_count,
+                                int peer_offset, unsigned long long* const* peer_flags, unsigned long long peer_step, int peer_rank,
+                                icr_workspace* ws, icr_stream stream) {
+    if (!images || !labels || !image_sizes || !params || (!rewards && !peer_rewards)) return fail(ICR_EINVAL, "null ptr");
     if (label_dtype != ICR_LABELS_I32 && label_dtype != ICR_LABELS_I64) return fail(ICR_EINVAL, "labels must be int32 or int64");
     if (B <= 0 || S <= 0) return fail(ICR_EINVAL, "B and S must be positive");
     if (int rc = check_shape(ws, B * S, H, W)) return rc;
     cudaStream_t st = (cudaStream_t)stream;
     Tables t = ws->t;
     t.V = B * S;
+    t.peer_rewards = peer_rewards; t.peer_count = peer_count; t.peer_offset = peer_offset;
+    t.peer_flags = peer_flags; t.peer_step = peer_step; t.peer_rank = peer_rank;
     const EstParams p = widen(params);
     const Inputs in{images, labels, label_dtype, S};
     ws->in = in;
@@ -182,6 +185,22 @@ int icr_compute_rewards(const float* images, const void* labels, int label_dtype
     if (!fused) ICR_CUDA(launch_reward(t, p, image_sizes, S, rewards, st), "reward");
     if (prof) cudaEventRecord(ws->ev[4], st);
     return ICR_OK;
+}
+
+int icr_compute_rewards(const float* images, const void* labels, int label_dtype, const double* image_sizes, int B, int S, int H,
+                        int W, const icr_params* params, double* rewards, icr_workspace* ws, icr_stream stream) {
+    if (!rewards) return fail(ICR_EINVAL, "null ptr");
+    return compute_rewards_impl(images, labels, label_dtype, image_sizes, B, S, H, W, params, rewards, nullptr, 0, 0, nullptr, 0, 0, ws, stream);
+}
+
+int icr_compute_rewards_gather(const float* images, const void* labels, int label_dtype, const double* image_sizes, int B, int S,
+                               int H, int W, const icr_params* params, double* rewards_local, double* const* gathered_of_rank_dev,
+                               unsigned long long* const* flags_of_rank_dev, unsigned long long step, int ranks, int rank,
+                               icr_workspace* ws, icr_stream stream) {
+    if (!gathered_of_rank_dev) return fail(ICR_EINVAL, "null ptr");
+    if (ranks <= 0 || rank < 0 || rank >= ranks) return fail(ICR_EINVAL, "rank must lie in [0, ranks)");
+    return compute_rewards_impl(images, labels, label_dtype, image_sizes, B, S, H, W, params, rewards_local, gathered_of_rank_dev, ranks,
+                                rank * B * S, flags_of_rank_dev, step, rank, ws, stream);
 }
 
 int icr_compute_rewards_host(const float* images_h, const void* labels_h, int label_dtype, const double* image_sizes_h,
@@ -411,7 +430,15 @@ int icr_ema_update(const double* rewards, int n, const double* sum_count, double
                    double* advantages, icr_stream stream) {
     if (!rewards || !state) return fail(ICR_EINVAL, "null ptr");
     if (n <= 0) return fail(ICR_EINVAL, "n must be positive");
-    ICR_CUDA(launch_ema(rewards, n, sum_count, momentum, state, advantages, (cudaStream_t)stream), "ema");
+    ICR_CUDA(launch_ema(rewards, n, sum_count, momentum, state, advantages, nullptr, 0, 0, (cudaStream_t)stream), "ema");
+    return ICR_OK;
+}
+
+int icr_ema_update_gathered(const double* gathered, int n, const unsigned long long* flags_local, int ranks, unsigned long long step,
+                            double momentum, double* state, double* advantages, icr_stream stream) {
+    if (!gathered || !state || !flags_local) return fail(ICR_EINVAL, "null ptr");
+    if (n <= 0 || ranks <= 0 || ranks > 1024) return fail(ICR_EINVAL, "n and ranks must be positive (ranks at most 1024)");
+    ICR_CUDA(launch_ema(gathered, n, nullptr, momentum, state, advantages, flags_local, ranks, step, (cudaStream_t)stream), "ema");
     return ICR_OK;
 }
 

@@ -166,7 +166,8 @@ __global__ void __launch_bounds__(BIG_T) big_kernel(Tables t, Inputs in, EstPara
     const int64_t HW = (int64_t)t.H * t.W;
     BigDebug none{};
     // maps without such a segment: their sizes all come from the estimate kernel; a warp per map does Rule W
-    if (rewards)
+    const bool do_rewards = rewards != nullptr || t.peer_rewards != nullptr;
+    if (do_rewards)
         for (int v = blockIdx.x * (BIG_T / 32) + (threadIdx.x >> 5); v < t.V; v += gridDim.x * (BIG_T / 32)) {
             const int2 mm = t.map_max[v];
             if (t.status[v] != ST_OK || !map_may_need_big_kernel(mm.x, mm.y, p.L_min))
@@ -193,7 +194,7 @@ __global__ void __launch_bounds__(BIG_T) big_kernel(Tables t, Inputs in, EstPara
                 block_segment(src, bb.x, bb.y, bb.z - bb.x + 1, bb.w - bb.y + 1, 4, p, filt, sizes + kk, none);
             }
         }
-        if (!rewards) continue;
+        if (!do_rewards) continue;
         __syncthreads();
         if (threadIdx.x == 0) {
             __threadfence();
@@ -207,6 +208,7 @@ __global__ void __launch_bounds__(BIG_T) big_kernel(Tables t, Inputs in, EstPara
         }
         __syncthreads();                                   // s_last is reused by the next pair
     }
+    signal_peers_when_grid_done(t, gridDim.x);
 }
 
 template <typename LT>

@@ -29,6 +29,16 @@ struct Tables {            // device pointers into the workspace, V label maps
     int32_t* big_done;     // [V] big-segment CTAs of a map that have finished (self-resetting)
     unsigned long long* slice_map_off;   // [V] byte offset of a map's first slice in the packed slice buffer (slices.cu)
     const double* clog2;   // [CLOG2_N] c*log2(c)
+    // multi-GPU gather fused into the reward writer (icr_compute_rewards_gather): the reward of map v also goes to
+    // peer_rewards[g][peer_offset + v] for every rank g -- plain stores into peer memory over NVLink.  NULL otherwise.
+    double* const* peer_rewards;
+    int peer_count, peer_offset;
+    // optional signalling in place of a barrier: when the last CTA of the reward-writing kernel is done, flag
+    // peer_flags[g][peer_rank] = peer_step is stored into every rank g (icr_reward.cuh: signal_peers_when_grid_done);
+    // the consumer (icr_ema_update_gathered) waits for the flags of all ranks.
+    unsigned long long* const* peer_flags;
+    unsigned long long peer_step;
+    int peer_rank;
     int V, H, W, Kmax;
 };
 
@@ -109,7 +119,8 @@ cudaError_t launch_single_segment(const uint8_t* img, int W, int H, int channels
                                   double* out, uint32_t* row_costs, uint8_t* filter_id, uint32_t* hist,
                                   unsigned long long* match, uint8_t* filter_scratch, cudaStream_t st);
 cudaError_t launch_ema(const double* rewards, int n, const double* sum_count, double momentum,
-                       double* state, double* adv, cudaStream_t st);
+                       double* state, double* adv, const unsigned long long* flags, int ranks, unsigned long long step,
+                       cudaStream_t st);
 cudaError_t launch_sum_count(const double* rewards, int n, double* sum_count, cudaStream_t st);
 cudaError_t run_selftest(int* mismatches);
 

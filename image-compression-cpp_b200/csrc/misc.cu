@@ -10,8 +10,8 @@ namespace icr {
 __global__ void __launch_bounds__(128) reward_kernel(Tables t, EstParams p, const double* __restrict__ image_sizes,
                                                       int S, double* __restrict__ rewards) {
     const int v = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
-    if (v >= t.V) return;
-    reward_of_map<false>(t, p, image_sizes, S, rewards, v, lane);
+    if (v < t.V) reward_of_map<false>(t, p, image_sizes, S, rewards, v, lane);
+    signal_peers_when_grid_done(t, gridDim.x);
 }
 
 cudaError_t launch_reward(const Tables& t, const EstParams& p, const double* image_sizes, int S, double* rewards, cudaStream_t st) {
@@ -111,9 +111,27 @@ __global__ void __launch_bounds__(1024) sum_count_kernel(const double* __restric
     if (threadIdx.x == 0) { out[0] = s; out[1] = (double)n; }
 }
 
+// flags != NULL: r is this rank's gathered vector, filled by all ranks' reward kernels through peer memory; wait until
+// every rank has signalled step `step` (bounded: a rank that never arrives poisons the baseline instead of hanging the GPU)
 __global__ void __launch_bounds__(1024) ema_kernel(const double* __restrict__ r, int n, const double* sum_count,
-                                                    double momentum, double* state, double* adv) {
+                                                    double momentum, double* state, double* adv,
+                                                    const unsigned long long* flags, int ranks, unsigned long long step) {
     __shared__ double sh[32];
+    __shared__ int s_timeout;
+    if (flags) {
+        if (threadIdx.x == 0) s_timeout = 0;
+        __syncthreads();
+        if ((int)threadIdx.x < ranks) {
+            const long long t0 = clock64();
+            unsigned long long seen;
+            do {
+                asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(seen) : "l"(flags + threadIdx.x) : "memory");
+            } while (seen < step && clock64() - t0 < 20000000000ll);         // ~10 s
+            if (seen < step) s_timeout = 1;
+        }
+        __syncthreads();
+        if (s_timeout) { if (threadIdx.x == 0) { state[0] = __longlong_as_double(0x7ff8000000000000ll); state[1] = 1.0; } return; }
+    }
     double s = 0.0;
     for (int i = threadIdx.x; i < n; i += blockDim.x) s += r[i];
     s = block_sum(s, sh);
@@ -142,8 +160,9 @@ cudaError_t launch_sum_count(const double* rewards, int n, double* sum_count, cu
     return cudaGetLastError();
 }
 
-cudaError_t launch_ema(const double* rewards, int n, const double* sum_count, double momentum, double* state, double* adv, cudaStream_t st) {
-    ema_kernel<<<1, 1024, 0, st>>>(rewards, n, sum_count, momentum, state, adv);
+cudaError_t launch_ema(const double* rewards, int n, const double* sum_count, double momentum, double* state, double* adv,
+                       const unsigned long long* flags, int ranks, unsigned long long step, cudaStream_t st) {
+    ema_kernel<<<1, 1024, 0, st>>>(rewards, n, sum_count, momentum, state, adv, flags, ranks, step);
     count_launch();
     return cudaGetLastError();
 }

@@ -26,10 +26,10 @@ class IcrParams(C.Structure):
 
 
 SYMBOLS = ["icr_last_error", "icr_version", "icr_default_params", "icr_workspace_bytes", "icr_workspace_create",
-           "icr_workspace_destroy", "icr_compute_rewards", "icr_compute_rewards_host", "icr_check",
+           "icr_workspace_destroy", "icr_compute_rewards", "icr_compute_rewards_gather", "icr_compute_rewards_host", "icr_check",
            "icr_label_capacity", "icr_segment_stats", "icr_counts_bboxes_from_compact_labels",
            "icr_estimate_png_size_segment", "icr_workspace_tables", "icr_debug_segment", "icr_slice_segment",
-           "icr_slices_prepare", "icr_slices_plan", "icr_slices_emit", "icr_reassemble_map", "icr_paste_slice", "icr_ema_update", "icr_reward_sum_count", "icr_selftest", "icr_launch_count", "icr_workspace_set_profile",
+           "icr_slices_prepare", "icr_slices_plan", "icr_slices_emit", "icr_reassemble_map", "icr_paste_slice", "icr_ema_update", "icr_ema_update_gathered", "icr_reward_sum_count", "icr_selftest", "icr_launch_count", "icr_workspace_set_profile",
            "icr_profile_read"]
 
 
@@ -360,6 +360,19 @@ def paste_slice(canvas, slice_hw4, x, y):
         _check(lib().icr_paste_slice(_ptr(canvas), C.c_int(W), C.c_int(H), _ptr(slice_hw4.contiguous()), C.c_int(x), C.c_int(y),
                                      C.c_int(w), C.c_int(h), _stream()))
     return canvas
+
+
+def ema_update_gathered(ema, peer, advantages=False):
+    """Rule E on the gathered vector of sharding.PeerGather's current step: the kernel first waits for every rank's flag."""
+    r = peer.gathered()
+    if ema.state is None:
+        ema.state = torch.zeros(2, dtype=torch.float64, device=r.device)
+    adv = torch.empty_like(r) if advantages else None
+    with torch.cuda.device(r.device):
+        _check(lib().icr_ema_update_gathered(_ptr(r), C.c_int(r.numel()), _ptr(peer.flags), C.c_int(peer.world),
+                                             C.c_ulonglong(peer.step), C.c_double(ema.momentum), _ptr(ema.state),
+                                             _ptr(adv) if advantages else None, _stream()))
+    return (ema.state[0], adv) if advantages else ema.state[0]
 
 
 def reward_sum_count(rewards):

@@ -4,7 +4,10 @@ include/ema_baseline.hpp:13 takes the mean of the whole batch).  Once every rank
 order, Rule E runs on it locally: one collective per step, and the EMA value is bit-identical to the single-GPU one
 because the sum runs over the same values in the same order.  `exchange` keeps the all-reduce of {sum, count} for
 callers that only want the statistics.
-torch.distributed is the transport (NCCL over NVLink on the GPU box, gloo in the CPU tests); nothing here computes."""
+torch.distributed is the transport (NCCL over NVLink on the GPU box, gloo in the CPU tests); nothing here computes.
+`PeerGather` removes even that collective on one NVLink box: every rank maps the others' gathered vectors
+(torch symmetric memory) and the reward kernel stores each reward straight into all of them
+(`icr_compute_rewards_gather`); a step then needs one device-side barrier instead of an all-gather."""
 import torch
 import torch.distributed as dist
 
@@ -50,3 +53,46 @@ def exchange(rewards_local, sum_count_local, B_total, group=None):
     if all(s == mx for s in sizes):
         return gathered, sc
     return torch.cat([gathered[r * mx:r * mx + sizes[r]] for r in range(world)]), sc
+
+
+class PeerGather:
+    """Gathered reward vectors of all ranks, mapped into every rank (symmetric memory over NVLink), plus one flag per
+    rank.  A step: `begin()` -> pass its three values to icr_compute_rewards_gather (the reward kernel stores every reward
+    into all ranks' vectors and, when its last CTA is done, sets this rank's flag everywhere) -> `EMABaseline.
+    update_gathered(peer)` waits on the device for all flags of the step, then reads the vector.  No collective, no
+    barrier kernel.  Two vectors alternate by step, so a rank that runs ahead cannot overwrite what a slower rank still
+    reads: it can only start step s+2 after it has seen every rank's flag of step s+1, which a rank raises after its
+    reader of step s (earlier on the same stream) has finished.
+    Raises if symmetric memory cannot be set up; callers fall back to `gather_rewards` (one NCCL all-gather)."""
+
+    def __init__(self, n_local, device, group=None):
+        import torch.distributed._symmetric_memory as symm_mem
+        group = group or dist.group.WORLD
+        self.world, self.rank, self.n_local = dist.get_world_size(group), dist.get_rank(group), int(n_local)
+        self.n_total = self.n_local * self.world
+        self.buf = symm_mem.empty(2 * self.n_total + self.world, dtype=torch.float64, device=device)
+        self.buf.zero_()
+        self.handle = symm_mem.rendezvous(self.buf, group.group_name)
+        ptrs = [int(p) for p in self.handle.buffer_ptrs]
+        i64 = dict(dtype=torch.int64, device=device)
+        self._targets = [torch.tensor([p + par * self.n_total * 8 for p in ptrs], **i64) for par in (0, 1)]
+        self.flag_ptrs = torch.tensor([p + 2 * self.n_total * 8 for p in ptrs], **i64)
+        self.flags = self.buf[2 * self.n_total:].view(torch.int64)           # this rank's flags, one per rank
+        self.step = 0
+        torch.cuda.synchronize(device)
+        self.handle.barrier(channel=0)                                       # every rank's zeros are in place
+        torch.cuda.synchronize(device)
+
+    def begin(self):
+        """Start a step: (device array of the ranks' gathered vectors, device array of the ranks' flag arrays, step)."""
+        self.step += 1
+        return self._targets[self.step & 1], self.flag_ptrs, self.step
+
+    def gathered(self):
+        """This rank's gathered vector of the current step (valid once the flags of the step are up)."""
+        par = self.step & 1
+        return self.buf[par * self.n_total:(par + 1) * self.n_total]
+
+    def barrier(self):
+        """Device-side barrier across ranks on the current stream (for callers that pass no flags)."""
+        self.handle.barrier(channel=0)

@@ -69,6 +69,23 @@ int icr_compute_rewards(const float* images, const void* labels, int label_dtype
                         const icr_params* params, double* rewards,
                         icr_workspace* ws, icr_stream stream);
 
+/* Sharded batches (one process per GPU; the reference is single-GPU and has no equivalent): the same call with the
+ * path's only exchange fused into the reward writer.  gathered_of_rank_dev is a DEVICE array of `ranks` pointers, entry g
+ * being rank g's gathered reward vector f64 [ranks*B*S] mapped into this process (CUDA IPC / symmetric memory over
+ * NVLink); the reward of local map v is stored at [rank*B*S + v] of every one of them, this rank's own included.
+ * rewards_local may be NULL.  flags_of_rank_dev (DEVICE array of `ranks` pointers to each rank's u64 [ranks] flag
+ * array, peer-mapped the same way; may be NULL): when this rank's last reward has been stored, flag [rank] of every
+ * rank is set to `step` (release at system scope), and icr_ema_update_gathered on the consumer side waits for the flags
+ * of all ranks -- no barrier kernel, no collective.  `step` must grow by one per call; the caller alternates two
+ * gathered vectors so that a fast rank cannot overwrite what a slow one still reads.  With flags NULL the caller
+ * separates steps with its own barrier across ranks. */
+int icr_compute_rewards_gather(const float* images, const void* labels, int label_dtype,
+                               const double* image_sizes, int B, int S, int H, int W,
+                               const icr_params* params, double* rewards_local,
+                               double* const* gathered_of_rank_dev,
+                               unsigned long long* const* flags_of_rank_dev, unsigned long long step,
+                               int ranks, int rank, icr_workspace* ws, icr_stream stream);
+
 /* Same through HOST buffers (pinned or pageable): H2D of images/labels/sizes, the path, D2H of
  * rewards, then a stream synchronise.  This is the call bench.py times as `e2e`.  Batches of 64 images
  * and more go over in four pieces, each copied on a second stream while the piece before it is
@@ -169,6 +186,11 @@ int icr_paste_slice(uint8_t* canvas_hw4, int W, int H, const uint8_t* slice_hw4,
 int icr_ema_update(const double* rewards, int n, const double* sum_count, double momentum,
                    double* state, double* advantages, icr_stream stream);
 int icr_reward_sum_count(const double* rewards, int n, double* sum_count, icr_stream stream);
+/* Rule E on a gathered vector filled through peer memory: first waits (on the device, bounded to ~10 s, after which the
+ * baseline becomes NaN) until flags_local[g] >= step for every rank g, then does what icr_ema_update does. */
+int icr_ema_update_gathered(const double* gathered, int n, const unsigned long long* flags_local, int ranks,
+                            unsigned long long step, double momentum, double* state, double* advantages,
+                            icr_stream stream);
 
 /* Exhaustive device self-test of the packed-byte filter arithmetic against scalar code
  * (all 2^24 Paeth triples, all Avg pairs, all cost bytes): *mismatches is a host int. Synchronous. */
