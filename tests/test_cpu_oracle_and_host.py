@@ -182,3 +182,9 @@ dist.destroy_process_group()
     mean = float(out.stdout.split("OK")[1].split()[0])
     v, _ = orc.ema_update(0.0, False, 0.99, np.arange(7) * 0.25 - 0.5)
     assert abs(mean - v) < 1e-15
+
+
+def test_exchange_classes_are_importable_without_a_gpu():
+    """PipelinedGather / PeerGather need CUDA to construct; their module must still import on a CPU box."""
+    from image_compression_cpp_b200 import sharding
+    assert callable(sharding.PipelinedGather) and callable(sharding.PeerGather) and sharding.shard_range(10, 4, 3) == (8, 10)
