@@ -35,40 +35,59 @@ void check_rc(int rc) {
 }  // namespace
 
 // ----------------------------------------------------------------------------------------------------- metadata.bin
+namespace {
+void put_le(std::vector<char>& out, uint64_t v, int bytes) {
+    for (int i = 0; i < bytes; ++i) out.push_back((char)((v >> (8 * i)) & 0xffu));
+}
+uint64_t get_le(const unsigned char* p, int bytes) {
+    uint64_t v = 0;
+    for (int i = 0; i < bytes; ++i) v |= (uint64_t)p[i] << (8 * i);
+    return v;
+}
+}  // namespace
+
 void write_metadata_binary(const std::vector<SliceMetadata>& metadata, const std::string& path, uint32_t image_width,
                            uint32_t image_height) {
-    std::vector<char> buf;
-    SliceRecordHeader header{0x534C4943u, (uint32_t)metadata.size(), image_width, image_height};
-    buf.insert(buf.end(), (const char*)&header, (const char*)&header + sizeof header);
+    std::vector<char> out;
+    out.reserve(icr_sidecar::kHeaderBytes + metadata.size() * (icr_sidecar::kRecordBytes + 16));
+    put_le(out, icr_sidecar::kMagic, 4);
+    put_le(out, (uint32_t)metadata.size(), 4);
+    put_le(out, image_width, 4);
+    put_le(out, image_height, 4);
     for (const SliceMetadata& m : metadata) {
-        SliceRecordFixed fixed{m.label, m.x, m.y, m.width, m.height, (uint16_t)m.filename.size()};
-        buf.insert(buf.end(), (const char*)&fixed, (const char*)&fixed + sizeof fixed);
-        buf.insert(buf.end(), m.filename.begin(), m.filename.end());
+        const int32_t fields[5] = {m.label, m.x, m.y, m.width, m.height};
+        for (int32_t f : fields) put_le(out, (uint32_t)f, 4);
+        put_le(out, (uint16_t)m.filename.size(), 2);                  // the reference truncates the length to 16 bits too
+        out.insert(out.end(), m.filename.begin(), m.filename.end());
     }
-    std::ofstream f(path, std::ios::binary);
-    f.write(buf.data(), (std::streamsize)buf.size());
+    std::ofstream f(path, std::ios::binary | std::ios::trunc);
+    f.write(out.data(), (std::streamsize)out.size());
 }
 
 std::vector<SliceMetadata> read_metadata_binary(const std::string& path, uint32_t& image_width, uint32_t& image_height) {
     std::ifstream f(path, std::ios::binary);
     if (!f) throw std::runtime_error("Cannot open metadata file");
-    SliceRecordHeader header{};
-    f.read((char*)&header, sizeof header);
-    if (header.magic != 0x534C4943u) throw std::runtime_error("Invalid metadata file (magic mismatch)");
-    image_width = header.original_width;
-    image_height = header.original_height;
-    std::vector<SliceMetadata> out;
-    out.reserve(header.count);
-    for (uint32_t i = 0; i < header.count; ++i) {
-        SliceRecordFixed fixed{};
-        f.read((char*)&fixed, sizeof fixed);
+    unsigned char head[icr_sidecar::kHeaderBytes] = {};
+    f.read((char*)head, sizeof head);
+    if (get_le(head, 4) != icr_sidecar::kMagic) throw std::runtime_error("Invalid metadata file (magic mismatch)");
+    const uint32_t count = (uint32_t)get_le(head + 4, 4);
+    image_width = (uint32_t)get_le(head + 8, 4);
+    image_height = (uint32_t)get_le(head + 12, 4);
+    std::vector<SliceMetadata> records;
+    for (uint32_t i = 0; i < count && f; ++i) {
+        unsigned char fixed[icr_sidecar::kRecordBytes] = {};
+        f.read((char*)fixed, sizeof fixed);
         SliceMetadata m;
-        m.label = fixed.label; m.x = fixed.x; m.y = fixed.y; m.width = fixed.width; m.height = fixed.height;
-        m.filename.assign(fixed.filename_len, '\0');
-        f.read(&m.filename[0], fixed.filename_len);
-        out.push_back(std::move(m));
+        m.label = (int32_t)get_le(fixed, 4);
+        m.x = (int32_t)get_le(fixed + 4, 4);
+        m.y = (int32_t)get_le(fixed + 8, 4);
+        m.width = (int32_t)get_le(fixed + 12, 4);
+        m.height = (int32_t)get_le(fixed + 16, 4);
+        m.filename.resize((size_t)get_le(fixed + 20, 2));
+        if (!m.filename.empty()) f.read(&m.filename[0], (std::streamsize)m.filename.size());
+        records.push_back(std::move(m));
     }
-    return out;
+    return records;
 }
 
 // ------------------------------------------------------------------------------------------------------ image_slicer
