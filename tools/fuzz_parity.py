@@ -103,6 +103,38 @@ def main():
         if not ok or rel > 1e-9:
             print("MISMATCH", recipe, "rel", rel, "tables ok", ok)
             sys.exit(1)
+        # the slices of the same call: a few of them against the oracle's Rule P, and the decoder round trip of map 0
+        ws.inputs = (ti, tl, ts)
+        swap = bool(rng.integers(0, 2))
+        buf, off = ws.slices(order=int(swap))
+        keys = ws.keys().cpu().numpy()
+        bufh, offh = buf.cpu().numpy(), off.cpu().numpy()
+        maps = tl.cpu().numpy().reshape(B * S, H, W)
+        f0 = 0
+        for v in range(B * S):
+            rgba = orc.chw3_f32_to_rgba(images[v // S])
+            comp, uniq = orc.compact_labels(maps[v])
+            for k in rng.choice(det["K"][v], size=min(3, det["K"][v]), replace=False):
+                x0, y0, x1, y1 = det["bboxes"][v, k]
+                w, h = x1 - x0 + 1, y1 - y0 + 1
+                sl = bufh[offh[f0 + k]:offh[f0 + k + 1]].reshape(h, w, 4)
+                ref = orc.slice_segment(rgba, comp, int(k), x0, y0, w, h)
+                if swap:
+                    ref = ref[..., [2, 1, 0, 3]]
+                if not np.array_equal(sl, ref) or keys[v, k] != uniq[k]:
+                    print("SLICE MISMATCH", recipe, "map", v, "segment", int(k))
+                    sys.exit(1)
+            f0 += det["K"][v]
+        if offh[-1] != bufh.size or len(offh) != f0 + 1:
+            print("SLICE PLAN MISMATCH", recipe)
+            sys.exit(1)
+        canvas = ws.reassemble_map(0, buf, off).cpu().numpy()
+        want_canvas = orc.chw3_f32_to_rgba(images[0])
+        if swap:
+            want_canvas = want_canvas[..., [2, 1, 0, 3]]
+        if not np.array_equal(canvas, want_canvas):
+            print("DECODER MISMATCH", recipe)
+            sys.exit(1)
         ws.close()
     print(f"fuzz ok: {iters} cases, seed {seed}, worst relative reward error {worst:.2e}, {time.time() - t0:.0f} s")
 
