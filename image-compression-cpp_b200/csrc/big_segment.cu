@@ -173,7 +173,14 @@ __global__ void __launch_bounds__(BIG_T) big_kernel(Tables t, Inputs in, EstPara
             if (t.status[v] != ST_OK || !map_may_need_big_kernel(mm.x, mm.y, p.L_min))
                 reward_of_map<false>(t, p, image_sizes, in.S, rewards, v, threadIdx.x & 31);
         }
-    for (int pair = blockIdx.x; pair < t.V * BIG_CTAS; pair += gridDim.x) {
+    // all pairs of this CTA are looked at side by side first: usually none needs work and the CTA is done after one round trip
+    int mine = 0;
+    for (int pair = blockIdx.x + threadIdx.x * gridDim.x; pair < t.V * BIG_CTAS; pair += BIG_T * gridDim.x) {
+        const int2 mm = t.map_max[pair / BIG_CTAS];
+        mine |= t.status[pair / BIG_CTAS] == ST_OK && map_may_need_big_kernel(mm.x, mm.y, p.L_min);
+    }
+    const bool any_work = __syncthreads_or(mine) != 0;
+    for (int pair = blockIdx.x; any_work && pair < t.V * BIG_CTAS; pair += gridDim.x) {
         const int v = pair / BIG_CTAS, part = pair % BIG_CTAS;
         const int2 mm = t.map_max[v];
         if (t.status[v] != ST_OK || !map_may_need_big_kernel(mm.x, mm.y, p.L_min)) continue;
