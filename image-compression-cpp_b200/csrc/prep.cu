@@ -120,11 +120,14 @@ __device__ __forceinline__ void sweep_runs(const LT* __restrict__ lab, int64_t H
 }
 
 // ---- sweep 1 on runs: the same head detection as sweep_runs; a head marks its label in the presence bitmap, feeds min/max and
-// appends one record {slot | (len-1) << 20, y << 16 | x} to the map's run list (one shared-memory atomic per warp and round).
-// With the list complete, Rule S needs no second pass over the pixels: sweep_list walks the records.
+// appends one record {slot | (len-1) << 20, y << 16 | x} to its warp's share of the map's run list (every warp owns
+// run_cap / warps records and counts in a register: no atomic, no exchange).  With the lists complete, Rule S needs no
+// second pass over the pixels: sweep_list walks the records, every warp its own.  Returns the warp's record count
+// (beyond `region` when the share overflowed: the caller then falls back to the pixel sweep).
 template <typename LT, int VEC>
-__device__ __forceinline__ void sweep_mark(const LT* __restrict__ lab, int64_t HW, int W, uint32_t* bitmap, uint32_t cmask, LT& lo, LT& hi,
-                                           uint2* __restrict__ runs, int run_cap, int* s_nruns) {
+__device__ __forceinline__ int sweep_mark(const LT* __restrict__ lab, int64_t HW, int W, uint32_t* bitmap, uint32_t cmask, LT& lo, LT& hi,
+                                          uint2* __restrict__ runs, int region) {
+    int wcount = 0;
     const int tid = threadIdx.x, lane = tid & 31;
     int64_t p = (int64_t)tid * VEC;
     int y = (int)(p / W), x = (int)(p - (int64_t)y * W);
@@ -154,9 +157,6 @@ __device__ __forceinline__ void sweep_mark(const LT* __restrict__ lab, int64_t H
         const int next_after = above ? nl * VEC + nfirst : __popc(inm) * VEC;
         uint32_t act;
         while ((act = __ballot_sync(0xffffffffu, hm != 0u)) != 0u) {
-            int rbase = 0;
-            if (lane == 0) rbase = atomicAdd(s_nruns, __popc(act));
-            rbase = __shfl_sync(0xffffffffu, rbase, 0);
             if (hm) {
                 const int i = __ffs(hm) - 1;
                 hm &= hm - 1;
@@ -168,18 +168,20 @@ __device__ __forceinline__ void sweep_mark(const LT* __restrict__ lab, int64_t H
                 lo = min(lo, lv); hi = max(hi, lv);
                 const uint32_t idx = (uint32_t)lv & cmask, bit = 1u << (idx & 31);
                 if (!(bitmap[idx >> 5] & bit)) atomicOr(&bitmap[idx >> 5], bit);
-                const int pos = rbase + __popc(act & lt_mask);
-                if (pos < run_cap) runs[pos] = make_uint2(idx | (uint32_t)(n - 1) << 20, (uint32_t)y << 16 | (uint32_t)(x + i));
+                const int pos = wcount + __popc(act & lt_mask);
+                if (pos < region) runs[pos] = make_uint2(idx | (uint32_t)(n - 1) << 20, (uint32_t)y << 16 | (uint32_t)(x + i));
             }
+            wcount += __popc(act);
         }
         x += stepx; y += stepy;
         if (x >= W) { x -= W; ++y; }
     }
+    return wcount;
 }
 
 template <bool SMEM, class RankSlot>
 __device__ __forceinline__ void sweep_list(const uint2* runs, int nruns, const StatsPtr& st, RankSlot rank_slot) {
-    for (int r = threadIdx.x; r < nruns; r += PREP_T) {
+    for (int r = threadIdx.x & 31; r < nruns; r += 32) {
         const uint2 rec = runs[r];                    // written by this CTA before a barrier: a plain (coherent) load
         const int n = (int)(rec.x >> 20) + 1, y = (int)(rec.y >> 16), xa = (int)(rec.y & 0xffffu);
         const int kc = (int)rank_slot(rec.x & 0xfffffu), k = kc * st.bst;
@@ -206,7 +208,8 @@ __global__ void __launch_bounds__(PREP_T, 2) prep_kernel(const LT* __restrict__ 
     __shared__ long long red_lo[PREP_T / 32], red_hi[PREP_T / 32];
     __shared__ uint32_t warp_tot[PREP_T / 32];
     __shared__ long long s_min;
-    __shared__ int s_bad, s_last, s_nruns, s_maxarea, s_maxw;
+    __shared__ int s_bad, s_last, s_over, s_maxarea, s_maxw;
+    __shared__ int s_wruns[PREP_T / 32];
 
     const int v = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int H = t.H, W = t.W;
@@ -217,15 +220,19 @@ __global__ void __launch_bounds__(PREP_T, 2) prep_kernel(const LT* __restrict__ 
     int bad = ST_OK;
 
     for (int i = tid; i < cap_words; i += PREP_T) bitmap[i] = 0;
-    if (tid == 0) { s_nruns = 0; s_maxarea = 0; s_maxw = 0; }
+    if (tid == 0) { s_over = 0; s_maxarea = 0; s_maxw = 0; }
     __syncthreads();
     // the run list serves the batch path; the compact-id output needs a pixel pass anyway
     const bool use_list = !COMPACT_OUT && t.run_cap > 0;
-    uint2* runs = t.runs + (int64_t)v * t.run_cap;
+    const int region = t.run_cap / (PREP_T / 32);                    // records a warp may write
+    uint2* runs = t.runs + (int64_t)v * t.run_cap + (int64_t)wid * region;
 
     // ---- sweep 1: min / max and the circular presence bitmap (plain read first: almost every bit is already set)
     LT lo = sizeof(LT) == 8 ? (LT)LLONG_MAX : (LT)INT_MAX, hi = sizeof(LT) == 8 ? (LT)LLONG_MIN : (LT)INT_MIN;
-    if (use_list) sweep_mark<LT, VEC>(lab, HW, W, bitmap, cmask, lo, hi, runs, t.run_cap, &s_nruns);
+    if (use_list) {
+        const int nw = sweep_mark<LT, VEC>(lab, HW, W, bitmap, cmask, lo, hi, runs, region);
+        if (lane == 0) { s_wruns[wid] = nw; if (nw > region) s_over = 1; }
+    }
     LT nxt[VEC];
     if (!use_list) load_labels<LT, VEC>(lab, (int64_t)tid * VEC, (int64_t)tid * VEC < HW, nxt);
     for (int64_t base = 0; base < HW && !use_list; base += (int64_t)PREP_T * VEC) {
@@ -308,7 +315,7 @@ __global__ void __launch_bounds__(PREP_T, 2) prep_kernel(const LT* __restrict__ 
             const StatsPtr st{stab, stab + KS_SMEM, stab + 2 * KS_SMEM, stab + 3 * KS_SMEM, stab + 4 * KS_SMEM, 1};
             for (int k = tid; k < K; k += PREP_T) { st.cnt[k] = 0; st.bx0[k] = W; st.by0[k] = H; st.bx1[k] = -1; st.by1[k] = -1; }
             __syncthreads();
-            if (use_list && s_nruns <= t.run_cap) sweep_list<true>(runs, s_nruns, st, rank_slot);
+            if (use_list && !s_over) sweep_list<true>(runs, s_wruns[wid], st, rank_slot);
             else sweep_runs<LT, VEC, true, COMPACT_OUT>(lab, HW, W, st, rank_of, compact_row);
             __syncthreads();
             int marea = 0, mw = 0;
@@ -325,7 +332,7 @@ __global__ void __launch_bounds__(PREP_T, 2) prep_kernel(const LT* __restrict__ 
             const StatsPtr st{g_cnt, g_bb, g_bb + 1, g_bb + 2, g_bb + 3, 4};
             for (int k = tid; k < K; k += PREP_T) { g_cnt[k] = 0; g_bb[4 * k] = W; g_bb[4 * k + 1] = H; g_bb[4 * k + 2] = -1; g_bb[4 * k + 3] = -1; }
             __syncthreads();
-            if (use_list && s_nruns <= t.run_cap) sweep_list<false>(runs, s_nruns, st, rank_slot);
+            if (use_list && !s_over) sweep_list<false>(runs, s_wruns[wid], st, rank_slot);
             else sweep_runs<LT, VEC, false, COMPACT_OUT>(lab, HW, W, st, rank_of, compact_row);
         }
     }
