@@ -3,8 +3,8 @@
 // (chunk = ceil(N/65536) >= L_min, src/png_size_estimator.cu:416-451), and (b) as the
 // pointer-level drop-in for estimate_png_size_masked_segment_to_output (:472-591).
 // Phase 1: a warp per bbox row, lanes along x, packed-byte costs, arg-min -> filter id per row.
-// Phase 2: a thread per reference chunk walks its bytes in stream order, recomputing residuals on
-// the fly (no residual buffer), feeding the shared-memory histogram and the run statistics.
+// Phase 2: the filtered stream goes through shared memory a tile at a time: a lane per pixel computes the residual
+// bytes and feeds the histogram, then a thread per reference chunk walks its bytes for the run statistics.
 // Entropy and mean follow the reference's reduction trees (:281-328) exactly.
 #include "icr_internal.h"
 #include "icr_pixel.cuh"
@@ -13,29 +13,33 @@
 namespace icr {
 
 constexpr int BIG_T = 256;
+constexpr int BIG_TILE_PX = 4096;       // residual words kept in shared memory per tile of the stream
 
 struct BigDebug { uint32_t* row_costs; uint8_t* filter_id; uint32_t* hist; unsigned long long* match; double* size; };
 
 template <typename LT>
 struct SrcPlanar {          // the batch layout: the caller's f32 planes + raw labels, masked by the segment's key
-    const float* img; const LT* lab; int64_t HW; int W; LT key;
+    const float *r, *g, *b; const LT* lab; int W; LT key;
+    __device__ SrcPlanar(const float* img, const LT* lab_, int64_t HW, int W_, LT key_)
+        : r(img), g(img + HW), b(img + 2 * HW), lab(lab_), W(W_), key(key_) {}
     __device__ __forceinline__ uint32_t px(int gy, int gx) const {
-        const int64_t i = (int64_t)gy * W + gx;
-        if (__ldg(lab + i) != key) return 0u;
-        const float r = __ldg(img + i), g = __ldg(img + HW + i), b = __ldg(img + 2 * HW + i);
-        auto tb = [](float v) { return (uint32_t)__float2int_rn(fminf(fmaxf(v, 0.f), 255.f)); };    // Rule C
-        return tb(r) | tb(g) << 8 | tb(b) << 16 | 0xff000000u;
+        // label and planes are asked for together (no branch on the label): the neighbours of a pixel then cost one memory
+        // round trip instead of two dependent ones each.  H*W < 2^31 (api.cu), so the pixel index is a 32-bit number.
+        const uint32_t i = (uint32_t)gy * (uint32_t)W + (uint32_t)gx;
+        const LT l = __ldg(lab + i);
+        const float fr = __ldg(r + i), fg = __ldg(g + i), fb = __ldg(b + i);
+        return l == key ? rgba_of(fr, fg, fb) : 0u;                                                  // Rule C, Rule P
     }
 };
 
 struct SrcRaw {             // the reference's layout: u8 [H,W,C] + compact int64 labels
     const uint8_t* img; const int64_t* lab; int W, C; int64_t k;
     __device__ __forceinline__ uint32_t px(int gy, int gx) const {
-        int64_t i = (int64_t)gy * W + gx;
-        if (lab[i] != k) return 0u;
+        const int64_t i = (int64_t)gy * W + gx;
+        const int64_t l = lab[i];
         uint32_t v = 0;
         for (int c = 0; c < C; ++c) v |= (uint32_t)img[i * C + c] << (8 * c);
-        return v;
+        return l == k ? v : 0u;
     }
 };
 
@@ -54,6 +58,7 @@ template <class Src>
 __device__ void block_segment(const Src& src, int x0, int y0, int w, int h, int C, const EstParams& p,
                               uint8_t* filt, double* out, const BigDebug& dbg) {
     __shared__ uint32_t s_hist[4 * 256];
+    __shared__ uint32_t s_tile[BIG_TILE_PX];
     __shared__ double s_red[256];
     __shared__ double s_Hc[4];
     __shared__ unsigned long long s_ms, s_mc, s_mls;
@@ -67,12 +72,17 @@ __device__ void block_segment(const Src& src, int x0, int y0, int w, int h, int 
         int f = 4;
         if (p.adaptive) {
             Costs5 c = {0, 0, 0, 0, 0};
-            for (int x = lane; x < w; x += 32) {
-                uint32_t cur = src.px(y0 + y, x0 + x);
-                uint32_t left = x > 0 ? src.px(y0 + y, x0 + x - 1) : 0u;
-                uint32_t up = y > 0 ? src.px(y0 + y - 1, x0 + x) : 0u;
-                uint32_t ul = (x > 0 && y > 0) ? src.px(y0 + y - 1, x0 + x - 1) : 0u;
-                add_costs(c, cur, left, up, ul);
+#pragma unroll 2
+            for (int xb = 0; xb < w; xb += 32) {         // the lane to the left holds this pixel's left and upper-left neighbours
+                const int x = xb + lane;
+                const uint32_t cur = x < w ? src.px(y0 + y, x0 + x) : 0u;
+                const uint32_t up = (x < w && y > 0) ? src.px(y0 + y - 1, x0 + x) : 0u;
+                uint32_t left = __shfl_up_sync(0xffffffffu, cur, 1), ul = __shfl_up_sync(0xffffffffu, up, 1);
+                if (lane == 0) {
+                    left = xb > 0 ? src.px(y0 + y, x0 + xb - 1) : 0u;
+                    ul = (xb > 0 && y > 0) ? src.px(y0 + y - 1, x0 + xb - 1) : 0u;
+                }
+                if (x < w) add_costs(c, cur, left, up, ul);
             }
             for (int o = 16; o; o >>= 1) {
                 c.none += __shfl_xor_sync(0xffffffffu, c.none, o);
@@ -91,38 +101,110 @@ __device__ void block_segment(const Src& src, int x0, int y0, int w, int h, int 
     }
     __syncthreads();
 
-    // ---- phase 2: stream walk, one reference chunk per thread step (Rules R, H, M)
+    // ---- phase 2: the filtered stream, tile by tile (Rules R, H, M).  A tile is a whole number of reference chunks and of
+    // pixels.  Step A: a lane per pixel in stream order -- coalesced loads, left neighbours by shuffle -- leaves the pixel's
+    // residual bytes in shared memory and feeds the histogram.  Step B: a thread per reference chunk walks its bytes there.
     const unsigned long long N = (unsigned long long)w * h * C;
     const unsigned long long chunk = (N + 65535ull) / 65536ull;
     const unsigned long long nchunks = (N + chunk - 1) / chunk;
     unsigned long long ms = 0, mc = 0;
-    for (unsigned long long t = tid; t < nchunks; t += BIG_T) {
-        const unsigned long long start = t * chunk;
-        const unsigned long long end = min(start + chunk, N);
-        long long pix = -1;
-        uint32_t r4 = 0;
-        int prev = -1, run = 0;
-        for (unsigned long long i = start; i < end; ++i) {
-            const long long pi = (long long)(i / (unsigned)C);
-            const int c = (int)(i - (unsigned long long)pi * C);
-            if (pi != pix) {
-                pix = pi;
-                const int y = (int)(pi / w), x = (int)(pi - (long long)y * w);
-                uint32_t cur = src.px(y0 + y, x0 + x);
-                uint32_t left = x > 0 ? src.px(y0 + y, x0 + x - 1) : 0u;
-                uint32_t up = y > 0 ? src.px(y0 + y - 1, x0 + x) : 0u;
-                uint32_t ul = (x > 0 && y > 0) ? src.px(y0 + y - 1, x0 + x - 1) : 0u;
-                r4 = residual4(filt[y], cur, left, up, ul);
+    if (chunk <= (unsigned long long)BIG_TILE_PX) {
+        const uint32_t n_px = (uint32_t)w * (uint32_t)h, ck = (uint32_t)chunk;
+        const uint32_t tile_px = ck * ((uint32_t)BIG_TILE_PX / ck);               // tile bytes = tile_px * C: chunks * C whole chunks
+        for (uint32_t p0 = 0; p0 < n_px; p0 += tile_px) {
+            const uint32_t here = min(tile_px, n_px - p0);
+#pragma unroll 2
+            for (uint32_t base = (uint32_t)(tid - lane); base < here; base += BIG_T) {
+                const uint32_t q = base + lane;
+                const bool in = q < here;
+                const uint32_t pi = p0 + (in ? q : 0u);
+                const int y = (int)(pi / (uint32_t)w), x = (int)(pi - (uint32_t)y * (uint32_t)w);
+                const uint32_t cur = in ? src.px(y0 + y, x0 + x) : 0u;
+                const uint32_t up = (in && y > 0) ? src.px(y0 + y - 1, x0 + x) : 0u;
+                uint32_t left = __shfl_up_sync(0xffffffffu, cur, 1), ul = __shfl_up_sync(0xffffffffu, up, 1);
+                if (lane == 0 && in && x > 0) {
+                    left = src.px(y0 + y, x0 + x - 1);
+                    ul = y > 0 ? src.px(y0 + y - 1, x0 + x - 1) : 0u;
+                }
+                if (x == 0) { left = 0u; ul = 0u; }
+                if (in) {
+                    const uint32_t r4 = residual4(filt[y], cur, left, up, ul);
+                    s_tile[q] = r4;
+                    for (int c = 0; c < C; ++c) atomicAdd(&s_hist[c * 256 + ((r4 >> (8 * c)) & 255u)], 1u);
+                }
             }
-            const int b = (int)((r4 >> (8 * c)) & 255u);
-            atomicAdd(&s_hist[c * 256 + b], 1u);
-            if (b == prev) { ++run; }
-            else {
-                if (prev >= 0 && run >= p.L_min) { ms += (unsigned long long)run; mc += 1; }
-                prev = b; run = 1;
+            __syncthreads();
+            const uint32_t bytes = here * (uint32_t)C;
+            if (C == 4 && (ck & 3u) == 0) {               // chunks of whole pixels: four bytes per word, no channel counter
+                const uint32_t wpc = ck >> 2;
+                for (uint32_t w0 = (uint32_t)tid * wpc; w0 < here; w0 += BIG_T * wpc) {
+                    const uint32_t w1 = min(w0 + wpc, here);
+                    int prev = -1, run = 0;
+                    for (uint32_t wi = w0; wi < w1; ++wi) {
+                        const uint32_t r4 = s_tile[wi];
+#pragma unroll
+                        for (int c = 0; c < 4; ++c) {
+                            const int bv = (int)((r4 >> (8 * c)) & 255u);
+                            if (bv == prev) { ++run; }
+                            else {
+                                if (prev >= 0 && run >= p.L_min) { ms += (unsigned long long)run; mc += 1; }
+                                prev = bv; run = 1;
+                            }
+                        }
+                    }
+                    if (run >= p.L_min) { ms += (unsigned long long)run; mc += 1; }
+                }
+            } else
+            for (uint32_t start = (uint32_t)tid * ck; start < bytes; start += BIG_T * ck) {
+                const uint32_t end = min(start + ck, bytes);
+                uint32_t px_i = start / (uint32_t)C;
+                int c = (int)(start - px_i * (uint32_t)C);
+                uint32_t r4 = s_tile[px_i];
+                int prev = -1, run = 0;
+                for (uint32_t i = start; i < end; ++i) {
+                    const int bv = (int)((r4 >> (8 * c)) & 255u);
+                    if (bv == prev) { ++run; }
+                    else {
+                        if (prev >= 0 && run >= p.L_min) { ms += (unsigned long long)run; mc += 1; }
+                        prev = bv; run = 1;
+                    }
+                    if (++c == C) { c = 0; if (i + 1 < end) r4 = s_tile[++px_i]; }
+                }
+                if (run >= p.L_min) { ms += (unsigned long long)run; mc += 1; }
             }
+            __syncthreads();
         }
-        if (run >= p.L_min) { ms += (unsigned long long)run; mc += 1; }
+    } else {
+        // chunks longer than a tile (segments beyond 2^28 bytes): a thread per chunk reads its pixels directly
+        for (unsigned long long t = tid; t < nchunks; t += BIG_T) {
+            const unsigned long long start = t * chunk;
+            const unsigned long long end = min(start + chunk, N);
+            const unsigned long long pi0 = start / (unsigned)C;
+            int c = (int)(start - pi0 * (unsigned)C);
+            int y = (int)(pi0 / (unsigned)w), x = (int)(pi0 - (unsigned long long)y * (unsigned)w);
+            bool fresh = true;
+            uint32_t r4 = 0;
+            int prev = -1, run = 0;
+            for (unsigned long long i = start; i < end; ++i) {
+                if (fresh) {
+                    fresh = false;
+                    uint32_t cur = src.px(y0 + y, x0 + x);
+                    uint32_t left = x > 0 ? src.px(y0 + y, x0 + x - 1) : 0u;
+                    uint32_t up = y > 0 ? src.px(y0 + y - 1, x0 + x) : 0u;
+                    uint32_t ul = (x > 0 && y > 0) ? src.px(y0 + y - 1, x0 + x - 1) : 0u;
+                    r4 = residual4(filt[y], cur, left, up, ul);
+                }
+                const int bv = (int)((r4 >> (8 * c)) & 255u);
+                atomicAdd(&s_hist[c * 256 + bv], 1u);
+                if (bv == prev) { ++run; }
+                else {
+                    if (prev >= 0 && run >= p.L_min) { ms += (unsigned long long)run; mc += 1; }
+                    prev = bv; run = 1;
+                }
+                if (++c == C) { c = 0; fresh = true; if (++x == w) { x = 0; ++y; } }
+            }
+            if (run >= p.L_min) { ms += (unsigned long long)run; mc += 1; }
+        }
     }
     if (ms) { atomicAdd(&s_ms, ms); atomicAdd(&s_mls, ms); }    // match_symbols == match_len_sum (:440-442)
     if (mc) atomicAdd(&s_mc, mc);
@@ -181,7 +263,7 @@ __global__ void __launch_bounds__(BIG_T) big_kernel(Tables t, Inputs in, EstPara
     }
     const bool any_work = __syncthreads_or(mine) != 0;
     for (int pair = blockIdx.x; any_work && pair < t.V * BIG_CTAS; pair += gridDim.x) {
-        const int v = pair / BIG_CTAS, part = pair % BIG_CTAS;
+        const int v = pair / BIG_CTAS, part = (pair + v) % BIG_CTAS;      // rotated: part 0 of every map must not land on the same CTAs
         const int2 mm = t.map_max[v];
         if (t.status[v] != ST_OK || !map_may_need_big_kernel(mm.x, mm.y, p.L_min)) continue;
         const int K = t.K[v];
@@ -196,8 +278,8 @@ __global__ void __launch_bounds__(BIG_T) big_kernel(Tables t, Inputs in, EstPara
             for (int kk = k0 + ((part - k0) % BIG_CTAS + BIG_CTAS) % BIG_CTAS; kk < kend; kk += BIG_CTAS) {
                 const int4 bb = __ldg(bbs + kk);
                 if (!flagged(bb, p.L_min)) continue;
-                SrcPlanar<LT> src{in.images + (int64_t)(v / in.S) * 3 * HW, static_cast<const LT*>(in.labels) + (int64_t)v * HW, HW, t.W,
-                                  (LT)t.keys[(int64_t)v * t.Kmax + kk]};
+                SrcPlanar<LT> src(in.images + (int64_t)(v / in.S) * 3 * HW, static_cast<const LT*>(in.labels) + (int64_t)v * HW, HW, t.W,
+                                  (LT)t.keys[(int64_t)v * t.Kmax + kk]);
                 block_segment(src, bb.x, bb.y, bb.z - bb.x + 1, bb.w - bb.y + 1, 4, p, filt, sizes + kk, none);
             }
         }
@@ -224,8 +306,8 @@ __global__ void __launch_bounds__(BIG_T) big_debug_kernel(Tables t, Inputs in, E
     if (!flagged(bb, p.L_min)) return;          // the warp path's debug kernel handles it
     __shared__ double scratch;
     const int64_t HW = (int64_t)t.H * t.W;
-    SrcPlanar<LT> src{in.images + (int64_t)(v / in.S) * 3 * HW, static_cast<const LT*>(in.labels) + (int64_t)v * HW, HW, t.W,
-                      (LT)t.keys[(int64_t)v * t.Kmax + k]};
+    SrcPlanar<LT> src(in.images + (int64_t)(v / in.S) * 3 * HW, static_cast<const LT*>(in.labels) + (int64_t)v * HW, HW, t.W,
+                      (LT)t.keys[(int64_t)v * t.Kmax + k]);
     block_segment(src, bb.x, bb.y, bb.z - bb.x + 1, bb.w - bb.y + 1, 4, p, t.big_filter, &scratch, dbg);
 }
 
@@ -240,7 +322,7 @@ cudaError_t launch_big(const Tables& t, const Inputs& in, const EstParams& p, co
     if (launched) *launched = false;
     if (!for_big_kernel(t.W, t.H, p.L_min)) return cudaSuccess;
     if (launched) *launched = true;
-    const int grid = min(t.V * BIG_CTAS, 148 * 2);
+    const int grid = min(t.V * BIG_CTAS, 148 * 4);
     if (in.label_dtype == ICR_LABELS_I64) big_kernel<int64_t><<<grid, BIG_T, 0, st>>>(t, in, p, image_sizes, rewards);
     else big_kernel<int32_t><<<grid, BIG_T, 0, st>>>(t, in, p, image_sizes, rewards);
     count_launch();
