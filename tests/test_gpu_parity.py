@@ -189,6 +189,17 @@ def test_rule_m_whole_image_bbox_512(icr, orc, dev):
     _check_batch(icr, orc, dev, images, labels, np.full(2, 300000.0), n_debug=2)
 
 
+@pytest.mark.parametrize("H,W", [(256, 300), (300, 300), (320, 340)])
+def test_rule_m_chunks_that_straddle_pixels(icr, orc, dev, H, W):
+    # whole-image bboxes of 76800 / 90000 / 108800 pixels: chunk = 5, 6, 7 bytes, so chunks cut through pixels and the
+    # stream tiles of the big-segment kernel end on a partial tile
+    images = np.stack([synth.image_f32_chw(f, H, W, 20 + f) for f in (1, 4)])
+    images[1, :, 40:200, 30:250] = 77.0                     # a flat area: long runs, matches in every chunk there
+    labels = np.zeros((2, H, W), np.int32)
+    labels[0, 100:140, 50:90] = 2
+    _check_batch(icr, orc, dev, images, labels, np.full(2, 250000.0), n_debug=2)
+
+
 def test_multi_label_maps_share_one_image(icr, orc, dev):
     images, labels, sizes = synth.make_multi_batch(B=3, S=4, H=64, W=80)
     ti, tl, ts = _to(dev, images, labels, sizes)

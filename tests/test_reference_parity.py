@@ -100,6 +100,27 @@ def test_single_segment_estimator_dropin(icr, ref, orc, dev, channels, adaptive)
         icr.estimate_png_size_masked_segment_to_output(torch.zeros((4, 4, 5), dtype=torch.uint8, device=dev), tl, tc, 0, 0, 0, 2, 2)
 
 
+@pytest.mark.parametrize("channels,H,W", [(1, 400, 420), (2, 300, 330), (3, 250, 300), (4, 300, 290)])
+def test_single_segment_estimator_dropin_with_match_chunks(icr, ref, dev, channels, H, W):
+    """Segments past 65536 stream bytes: chunk = 3, 4, 4, 6 bytes here, not a whole number of pixels, so Rule M's run
+    statistics (src/png_size_estimator.cu:416-451) cross pixel and tile boundaries of the big-segment kernel."""
+    rng = np.random.default_rng(10 + channels)
+    img = np.ascontiguousarray(np.concatenate([synth.image_u8(5, H, W, 4), rng.integers(0, 256, (H, W, 1), dtype=np.uint8)], 2)[:, :, :channels])
+    img[60:200, 40:240] = 93                                  # flat area: runs well past L_min
+    lab = np.zeros((H, W), np.int64)
+    lab[10:40, 10:50] = 1
+    counts = np.bincount(lab.reshape(-1), minlength=2).astype(np.int32)
+    timg, tl, tc = torch.from_numpy(img).to(dev), torch.from_numpy(lab).to(dev), torch.from_numpy(counts).to(dev)
+    for L_min in (4, 2):
+        want = torch.zeros(1, dtype=torch.float64, device=dev)
+        rc = ref.ref_estimate_segment(C.c_void_p(timg.data_ptr()), W, H, channels, C.c_void_p(tl.data_ptr()), C.c_void_p(tc.data_ptr()),
+                                      C.c_int64(0), 0, 0, W, H, 0, 1, L_min, C.c_float(0.012167), C.c_float(18.0), C.c_float(0.1),
+                                      C.c_double(9.308622), 1, C.c_void_p(want.data_ptr()))
+        assert rc == 0, ref.ref_last_error()
+        got = icr.estimate_png_size_masked_segment_to_output(timg, tl, tc, 0, 0, 0, W, H, L_min=L_min, adaptive_filter=True)
+        assert torch.allclose(got, want, rtol=RTOL, atol=0), (channels, L_min, got, want)
+
+
 def test_ema_baseline_and_advantage(icr, orc, dev):
     rng = np.random.default_rng(5)
     ema = icr.EMABaseline(0.99)
