@@ -3,6 +3,7 @@
 // (src/image_slicer.cpp:48-74, one std::async per label at :98-100).  Here the counts and bboxes of the batch are
 // already in the workspace tables, so one launch plans where every slice goes in one packed buffer and one launch
 // writes all of them; the decoder side pastes slices where alpha > 0 (src/reassemble.cpp:75-107).
+#include <algorithm>
 #include "icr_internal.h"
 #include "icr_pixel.cuh"
 
@@ -79,65 +80,75 @@ __global__ void __launch_bounds__(256) plan_offsets_kernel(Tables t, const unsig
     }
 }
 
-// map of flat segment f, found by the 32 lanes together (seg_prefix is ascending)
-__device__ __forceinline__ int map_of_segment(const int32_t* __restrict__ sp, int V, int flat, int lane) {
-    int lo = 0, n = V;
-    while (n > 1) {
-        const int step = (n + 31) >> 5;
-        const int idx = lo + (lane + 1) * step;
-        const bool le = idx < lo + n && __ldg(sp + idx) <= flat;
-        const int c = __popc(__ballot_sync(0xffffffffu, le));
-        lo += c * step;
-        n = min(step, n - c * step);
-    }
-    return lo;
-}
-
 // ---- emit (Rule C + Rule P): one CTA per segment, threads along the slice's pixels in row-major order: the slice is
 // contiguous in the packed buffer, so stores are fully coalesced and the loads are row fragments of the three planes and
-// the label map.
+// the label map.  CTAs are dealt to (map, segment) pairs directly, so no CTA has to search the flat work list for its
+// map: with at least as many maps as CTAs a CTA takes whole maps, otherwise the CTAs of one residue class share a map
+// and stride over its segments.  The table row of a CTA's next segment is requested before the pixels of the current
+// one, so a segment costs one memory round trip (its pixels) instead of a chain of look-ups followed by the pixels.
+template <typename LT>
+struct SliceRow { int4 bb; LT key; unsigned long long o; };
+
+template <typename LT>
+__device__ __forceinline__ SliceRow<LT> slice_row(const Tables& t, const unsigned long long* __restrict__ offsets, int v, int f0, int k) {
+    SliceRow<LT> r;
+    const int64_t row = (int64_t)v * t.Kmax + k;
+    r.bb = __ldg(t.bboxes + row);
+    r.key = (LT)__ldg(t.keys + row);
+    r.o = __ldg(offsets + f0 + k) >> 2;
+    return r;
+}
+
 template <typename LT, bool SWAP>
 __global__ void __launch_bounds__(EMIT_T) slice_emit_kernel(Tables t, Inputs in, const unsigned long long* __restrict__ offsets,
                                                              uint32_t* __restrict__ out, unsigned long long cap_px) {
-    const int lane = threadIdx.x & 31;
-    const int total = __ldg(t.seg_prefix + t.V);
     const int64_t HW = (int64_t)t.H * t.W;
-    for (int flat = blockIdx.x; flat < total; flat += gridDim.x) {
-        const int v = map_of_segment(t.seg_prefix, t.V, flat, lane);
-        const int64_t row = (int64_t)v * t.Kmax + (flat - __ldg(t.seg_prefix + v));
-        const int4 bb = __ldg(t.bboxes + row);
-        const int w = bb.z - bb.x + 1, h = bb.w - bb.y + 1;
-        if (w <= 0 || h <= 0) continue;
-        const unsigned long long o = __ldg(offsets + flat) >> 2;
-        if (o + (unsigned long long)w * h > cap_px) continue;          // the host entry has checked the capacity already
-        const LT key = (LT)__ldg(t.keys + row);
-        const float* __restrict__ img = in.images + (int64_t)(v / in.S) * 3 * HW + (int64_t)bb.y * t.W + bb.x;
-        const LT* __restrict__ lab = static_cast<const LT*>(in.labels) + (int64_t)v * HW + (int64_t)bb.y * t.W + bb.x;
-        uint32_t* __restrict__ dst = out + o;
-        // lanes take the bbox pixels in row-major order, four independent pixels per lane in flight; all four loads of a
-        // pixel are issued together (the planes are read for masked-out pixels too: one latency instead of two)
-        const int n = w * h;                                       // the warp path's and the big kernel's bboxes are below 2^31 pixels
-        const float rw = 1.0f / (float)w;
-        constexpr int U = 4;
-        for (int i0 = threadIdx.x; i0 < n; i0 += EMIT_T * U) {
-            float c0[U], c1[U], c2[U];
-            LT l[U];
+    // the grid is P consecutive CTAs for each of the V maps (launch_slice_emit): CTA c strides over the segments of map c / P
+    const int nsub = gridDim.x / t.V, sub = blockIdx.x % nsub;
+    {
+        const int v = blockIdx.x / nsub;
+        const int f0 = __ldg(t.seg_prefix + v), K = __ldg(t.seg_prefix + v + 1) - f0;      // K = 0 for a map that failed
+        if (sub >= K) return;
+        const float* __restrict__ img_v = in.images + (int64_t)(v / in.S) * 3 * HW;
+        const LT* __restrict__ lab_v = static_cast<const LT*>(in.labels) + (int64_t)v * HW;
+        SliceRow<LT> nx = slice_row<LT>(t, offsets, v, f0, sub);
+        for (int k = sub; k < K; k += nsub) {
+            const SliceRow<LT> cur = nx;
+            if (k + nsub < K) nx = slice_row<LT>(t, offsets, v, f0, k + nsub);
+            const int4 bb = cur.bb;
+            const int w = bb.z - bb.x + 1, h = bb.w - bb.y + 1;
+            if (w <= 0 || h <= 0) continue;
+            if (cur.o + (unsigned long long)w * h > cap_px) continue;      // the host entry has checked the capacity already
+            const LT key = cur.key;
+            const int base = bb.y * t.W + bb.x;                        // a map has fewer than 2^31 pixels (icr_workspace_create)
+            const float* __restrict__ img = img_v + base;
+            const LT* __restrict__ lab = lab_v + base;
+            uint32_t* __restrict__ dst = out + cur.o;
+            // lanes take the bbox pixels in row-major order, four independent pixels per lane in flight; all four loads of
+            // a pixel are issued together (the planes are read for masked-out pixels too: one latency instead of two)
+            const int n = w * h;                                       // the warp path's and the big kernel's bboxes are below 2^31 pixels
+            const float rw = 1.0f / (float)w;
+            constexpr int U = 4;
+            for (int i0 = threadIdx.x; i0 < n; i0 += EMIT_T * U) {
+                float c0[U], c1[U], c2[U];
+                LT l[U];
 #pragma unroll
-            for (int u = 0; u < U; ++u) {
-                const int i = i0 + u * EMIT_T;
-                if (i < n) {
-                    int y = __float2int_rz(((float)i + 0.5f) * rw);        // i / w; corrected below where the float estimate is off by one
-                    y += (y + 1) * w <= i;
-                    y -= y * w > i;
-                    const int64_t g = (int64_t)y * t.W + (i - y * w);
-                    l[u] = lab[g];
-                    c0[u] = __ldg(img + g); c1[u] = __ldg(img + HW + g); c2[u] = __ldg(img + 2 * HW + g);
+                for (int u = 0; u < U; ++u) {
+                    const int i = i0 + u * EMIT_T;
+                    if (i < n) {
+                        int y = __float2int_rz(((float)i + 0.5f) * rw);        // i / w; corrected below where the float estimate is off by one
+                        y += (y + 1) * w <= i;
+                        y -= y * w > i;
+                        const int g = y * t.W + (i - y * w);
+                        l[u] = lab[g];
+                        c0[u] = __ldg(img + g); c1[u] = __ldg(img + HW + g); c2[u] = __ldg(img + 2 * HW + g);
+                    }
                 }
-            }
 #pragma unroll
-            for (int u = 0; u < U; ++u) {
-                const int i = i0 + u * EMIT_T;
-                if (i < n) dst[i] = l[u] == key ? (SWAP ? rgba_of(c2[u], c1[u], c0[u]) : rgba_of(c0[u], c1[u], c2[u])) : 0u;
+                for (int u = 0; u < U; ++u) {
+                    const int i = i0 + u * EMIT_T;
+                    if (i < n) dst[i] = l[u] == key ? (SWAP ? rgba_of(c2[u], c1[u], c0[u]) : rgba_of(c0[u], c1[u], c2[u])) : 0u;
+                }
             }
         }
     }
@@ -155,7 +166,13 @@ cudaError_t launch_slice_plan(const Tables& t, unsigned long long* offsets, long
 
 cudaError_t launch_slice_emit(const Tables& t, const Inputs& in, const unsigned long long* offsets, uint8_t* out, size_t cap,
                               int swap, cudaStream_t st) {
-    const int grid = 148 * 16;
+    if (t.V <= 0) return cudaSuccess;
+    const long long resident = 148 * 12;                            // CTAs the machine holds at once (40 registers, 128 threads)
+    const long long map_bytes = (long long)t.H * t.W * (12 + (in.label_dtype == ICR_LABELS_I64 ? 8 : 4));
+    const long long in_flight = std::max(1ll, (48ll << 20) / std::max(1ll, map_bytes));      // maps that share the L2 comfortably
+    long long P = std::min(1024ll, (resident + in_flight - 1) / in_flight);                  // CTAs per map
+    while (P > 1 && P * t.V > (1ll << 30)) P >>= 1;
+    const int grid = (int)(P * t.V);
     uint32_t* o = reinterpret_cast<uint32_t*>(out);
     const unsigned long long cap_px = cap / 4;
     if (in.label_dtype == ICR_LABELS_I64) {
