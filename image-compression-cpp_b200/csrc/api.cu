@@ -415,7 +415,14 @@ int icr_reassemble_map(icr_workspace* ws, int v, const unsigned long long* offse
                        uint8_t* canvas_hw4, icr_stream stream) {
     if (!ws || !offsets_dev || !slices_dev || !canvas_hw4) return fail(ICR_EINVAL, "null ptr");
     if (v < 0 || v >= ws->t.V) return fail(ICR_EINVAL, "label map index out of range");
-    ICR_CUDA(launch_reassemble(ws->t, v, offsets_dev, slices_dev, canvas_hw4, (cudaStream_t)stream), "reassemble");
+    ICR_CUDA(launch_reassemble(ws->t, v, 1, offsets_dev, slices_dev, canvas_hw4, (cudaStream_t)stream), "reassemble");
+    return ICR_OK;
+}
+
+int icr_reassemble_batch(icr_workspace* ws, const unsigned long long* offsets_dev, const uint8_t* slices_dev,
+                         uint8_t* canvases_vhw4, icr_stream stream) {
+    if (!ws || !offsets_dev || !slices_dev || !canvases_vhw4) return fail(ICR_EINVAL, "null ptr");
+    ICR_CUDA(launch_reassemble(ws->t, 0, ws->t.V, offsets_dev, slices_dev, canvases_vhw4, (cudaStream_t)stream), "reassemble batch");
     return ICR_OK;
 }
 

@@ -109,8 +109,8 @@ cudaError_t launch_slice_plan(const Tables& t, unsigned long long* offsets, long
                               cudaStream_t st);
 cudaError_t launch_slice_emit(const Tables& t, const Inputs& in, const unsigned long long* offsets, uint8_t* out, size_t cap,
                               int swap, cudaStream_t st);
-cudaError_t launch_reassemble(const Tables& t, int v, const unsigned long long* offsets, const uint8_t* slices, uint8_t* canvas,
-                              cudaStream_t st);
+cudaError_t launch_reassemble(const Tables& t, int v0, int nmaps, const unsigned long long* offsets, const uint8_t* slices,
+                              uint8_t* canvases, cudaStream_t st);
 cudaError_t launch_paste(uint8_t* canvas, int W, int H, const uint8_t* slice, int x, int y, int w, int h, cudaStream_t st);
 cudaError_t launch_compact_stats(const int64_t* labels, int H, int W, int K, int32_t* counts,
                                  int32_t* bboxes, cudaStream_t st);

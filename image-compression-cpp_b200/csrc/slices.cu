@@ -188,20 +188,43 @@ cudaError_t launch_slice_emit(const Tables& t, const Inputs& in, const unsigned 
 
 // ---- decoder: paste where alpha > 0 (src/reassemble.cpp:75-107).  All slices of one label map in one launch: the
 // segments of a partition do not overlap, so the order of the pastes does not matter.
-__global__ void __launch_bounds__(EMIT_T) reassemble_kernel(Tables t, int v, const unsigned long long* __restrict__ offsets,
-                                                             const uint32_t* __restrict__ slices, uint32_t* __restrict__ canvas) {
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+// The grid is P consecutive CTAs per map, as in the emit: `v0` is the first map and canvases lie HW*4 bytes apart, so
+// one map (icr_reassemble_map) and the whole batch (icr_reassemble_batch) are the same launch.
+__global__ void __launch_bounds__(EMIT_T) reassemble_kernel(Tables t, int v0, int P, const unsigned long long* __restrict__ offsets,
+                                                             const uint32_t* __restrict__ slices, uint32_t* __restrict__ canvases) {
+    const int v = v0 + blockIdx.x / P;
+    uint32_t* __restrict__ canvas = canvases + (int64_t)(blockIdx.x / P) * t.H * t.W;
     const int K = t.status[v] == ST_OK ? t.K[v] : 0;
     const int f0 = t.seg_prefix[v];
-    for (int k = blockIdx.x; k < K; k += gridDim.x) {
+    for (int k = blockIdx.x % P; k < K; k += P) {
         const int4 bb = t.bboxes[(int64_t)v * t.Kmax + k];
         const int w = bb.z - bb.x + 1, h = bb.w - bb.y + 1;
+        if (w <= 0 || h <= 0) continue;
         const uint32_t* __restrict__ src = slices + (offsets[f0 + k] >> 2);
-        for (int y = warp; y < h; y += EMIT_T / 32)
-            for (int x = lane; x < w; x += 32) {
-                const uint32_t px = src[(int64_t)y * w + x];
-                if (px >> 24) canvas[(int64_t)(bb.y + y) * t.W + bb.x + x] = px;
+        uint32_t* __restrict__ dst = canvas + (int64_t)bb.y * t.W + bb.x;
+        // threads along the slice's pixels in row-major order (the slice is contiguous: coalesced loads, all lanes busy
+        // whatever the width), four independent pixels per thread in flight
+        const int n = w * h;
+        const float rw = 1.0f / (float)w;
+        constexpr int U = 4;
+        for (int i0 = threadIdx.x; i0 < n; i0 += EMIT_T * U) {
+            uint32_t px[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int i = i0 + u * EMIT_T;
+                px[u] = i < n ? __ldg(src + i) : 0u;
             }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int i = i0 + u * EMIT_T;
+                if (px[u] >> 24) {
+                    int y = __float2int_rz(((float)i + 0.5f) * rw);        // i / w, corrected where the float estimate is off by one
+                    y += (y + 1) * w <= i;
+                    y -= y * w > i;
+                    dst[y * t.W + (i - y * w)] = px[u];
+                }
+            }
+        }
     }
 }
 
@@ -216,12 +239,20 @@ __global__ void __launch_bounds__(256) paste_kernel(uint32_t* __restrict__ canva
         }
 }
 
-cudaError_t launch_reassemble(const Tables& t, int v, const unsigned long long* offsets, const uint8_t* slices, uint8_t* canvas,
-                              cudaStream_t st) {
-    cudaError_t e = cudaMemsetAsync(canvas, 0, (size_t)t.H * t.W * 4, st);        // cv::Scalar(0,0,0,0), :50
+cudaError_t launch_reassemble(const Tables& t, int v0, int nmaps, const unsigned long long* offsets, const uint8_t* slices,
+                              uint8_t* canvases, cudaStream_t st) {
+    if (nmaps <= 0) return cudaSuccess;
+    const size_t map_bytes = (size_t)t.H * t.W * 4;
+    cudaError_t e = cudaMemsetAsync(canvases, 0, map_bytes * (size_t)nmaps, st);   // cv::Scalar(0,0,0,0), :50
     if (e != cudaSuccess) return e;
-    reassemble_kernel<<<148 * 4, EMIT_T, 0, st>>>(t, v, offsets, reinterpret_cast<const uint32_t*>(slices),
-                                                   reinterpret_cast<uint32_t*>(canvas));
+    // CTAs per map: enough that the maps in flight (canvas + slices, ~2.5x the canvas) share the L2, see launch_slice_emit
+    const long long resident = 148 * 16;
+    const long long in_flight = std::max(1ll, (48ll << 20) / std::max<long long>(1, (long long)map_bytes * 5 / 2));
+    long long P = std::min(1024ll, (resident + in_flight - 1) / in_flight);
+    if (nmaps == 1) P = 148 * 4;
+    while (P > 1 && P * nmaps > (1ll << 30)) P >>= 1;
+    reassemble_kernel<<<(unsigned)(P * nmaps), EMIT_T, 0, st>>>(t, v0, (int)P, offsets, reinterpret_cast<const uint32_t*>(slices),
+                                                                reinterpret_cast<uint32_t*>(canvases));
     count_launch();
     return cudaGetLastError();
 }

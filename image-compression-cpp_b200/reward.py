@@ -29,7 +29,7 @@ SYMBOLS = ["icr_last_error", "icr_version", "icr_default_params", "icr_workspace
            "icr_workspace_destroy", "icr_compute_rewards", "icr_compute_rewards_gather", "icr_compute_rewards_host", "icr_check",
            "icr_label_capacity", "icr_segment_stats", "icr_counts_bboxes_from_compact_labels",
            "icr_estimate_png_size_segment", "icr_workspace_tables", "icr_debug_segment", "icr_slice_segment",
-           "icr_slices_prepare", "icr_slices_plan", "icr_slices_emit", "icr_reassemble_map", "icr_paste_slice", "icr_ema_update", "icr_ema_update_gathered", "icr_reward_sum_count", "icr_selftest", "icr_launch_count", "icr_workspace_set_profile",
+           "icr_slices_prepare", "icr_slices_plan", "icr_slices_emit", "icr_reassemble_map", "icr_reassemble_batch", "icr_paste_slice", "icr_ema_update", "icr_ema_update_gathered", "icr_reward_sum_count", "icr_selftest", "icr_launch_count", "icr_workspace_set_profile",
            "icr_profile_read"]
 
 
@@ -163,6 +163,13 @@ class Workspace:
         with torch.cuda.device(self.device):
             _check(lib().icr_reassemble_map(self._h, C.c_int(v), _ptr(offsets), _ptr(buf), _ptr(canvas), _stream()))
         return canvas
+
+    def reassemble_batch(self, buf, offsets):
+        """All V label maps of the last batch at once: canvases u8 [V,H,W,4], one clear and one launch."""
+        canvases = torch.empty((self.V, self.H, self.W, 4), dtype=torch.uint8, device=self.device)
+        with torch.cuda.device(self.device):
+            _check(lib().icr_reassemble_batch(self._h, _ptr(offsets), _ptr(buf), _ptr(canvases), _stream()))
+        return canvases
 
     def close(self):
         if self._h:

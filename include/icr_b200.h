@@ -171,10 +171,14 @@ int icr_slices_emit(icr_workspace* ws, const unsigned long long* offsets_dev, ui
 
 /* ---- decoder side (src/reassemble.cpp:50-107): canvas u8 [H,W,4] starts at (0,0,0,0) and receives a slice where its
  * alpha > 0.  icr_reassemble_map clears the canvas and pastes every slice of label map v of the planned buffer in one
- * launch; icr_paste_slice pastes one slice from anywhere (a decoded file), clipped to the canvas, and leaves the rest of
+ * launch; icr_reassemble_batch does the same for all V label maps of the workspace's last batch at once (canvases u8
+ * [V,H,W,4]: one clear and one launch instead of V of each; the reference decodes one image per process run);
+ * icr_paste_slice pastes one slice from anywhere (a decoded file), clipped to the canvas, and leaves the rest of
  * the canvas alone -- pastes issued on one stream keep the reference's sequential order. */
 int icr_reassemble_map(icr_workspace* ws, int v, const unsigned long long* offsets_dev, const uint8_t* slices_dev,
                        uint8_t* canvas_hw4, icr_stream stream);
+int icr_reassemble_batch(icr_workspace* ws, const unsigned long long* offsets_dev, const uint8_t* slices_dev,
+                         uint8_t* canvases_vhw4, icr_stream stream);
 int icr_paste_slice(uint8_t* canvas_hw4, int W, int H, const uint8_t* slice_hw4, int x, int y, int w, int h,
                     icr_stream stream);
 

@@ -160,5 +160,7 @@ def test_slices_of_odd_shapes(icr, orc, dev, H, W):
     ws = _batch(icr, dev, images, labels, np.full(3, 500.0), prepare_only=True)
     buf, off = _compare_with_slicer(icr, orc, ws, images, labels)
     tb, to = torch.from_numpy(buf).to(dev), torch.from_numpy(off).to(dev)
+    batch = ws.reassemble_batch(tb, to).cpu().numpy()              # all maps in one launch: the same canvases
     for v in range(3):
         assert np.array_equal(ws.reassemble_map(v, tb, to).cpu().numpy(), orc.chw3_f32_to_rgba(images[v]))
+        assert np.array_equal(batch[v], orc.chw3_f32_to_rgba(images[v]))

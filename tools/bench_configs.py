@@ -102,6 +102,40 @@ def run(name, images, labels, sizes, pool_reps, steps=10):
                       "emit_hbm_GBps": hbm_bytes / (te * 1e-3) / 1e9, "emit_frac_of_hbm_peak": hbm_bytes / (te * 1e-3) / 1e9 / hbm_peak(),
                       "emit_logical_GBps": (nbytes * 5) / (te * 1e-3) / 1e9, "images_per_sec": B / ((tp + te) * 1e-3),
                       "note": "hbm bytes = every input plane once + 4 B written per bbox pixel; logical = 16 B read + 4 B written per bbox pixel"}))
+    # the decoder row: every slice of a label map pasted back into its canvas (one clear + one launch per map)
+    nmaps = min(B * S, 64)
+    canvas = torch.empty((nmaps, H, W, 4), dtype=torch.uint8, device=dev)
+    td = 0.0
+    for i in range(steps + 2):
+        ev[0].record()
+        for v in range(nmaps):
+            rc = L.icr_reassemble_map(ws.handle, v, C.c_void_p(offsets.data_ptr()), C.c_void_p(buf.data_ptr()), C.c_void_p(canvas[v].data_ptr()), st)
+        ev[1].record()
+        assert rc == 0, L.icr_last_error()
+        torch.cuda.synchronize()
+        if i >= 2:
+            td += ev[0].elapsed_time(ev[1]) / steps
+    # ... and the whole batch in one clear + one launch
+    all_canvas = torch.empty((B * S, H, W, 4), dtype=torch.uint8, device=dev)
+    tb = 0.0
+    for i in range(steps + 2):
+        ev[0].record()
+        rc = L.icr_reassemble_batch(ws.handle, C.c_void_p(offsets.data_ptr()), C.c_void_p(buf.data_ptr()), C.c_void_p(all_canvas.data_ptr()), st)
+        ev[1].record()
+        assert rc == 0, L.icr_last_error()
+        torch.cuda.synchronize()
+        if i >= 2:
+            tb += ev[0].elapsed_time(ev[1]) / steps
+    assert torch.equal(all_canvas[:nmaps], canvas)
+    dec_bytes = nbytes + 2 * all_canvas.numel()                   # slices read, canvases cleared and written
+    want_img = orc.chw3_f32_to_rgba(images[0])
+    ok = bool(np.array_equal(canvas[0].cpu().numpy(), want_img))
+    print(json.dumps({"config": name + " -- decoder", "maps": nmaps, "ms_per_map": td / nmaps, "maps_per_sec": nmaps / (td * 1e-3),
+                      "canvas_GBps": nmaps * H * W * 4 / (td * 1e-3) / 1e9,
+                      "batch_ms": tb, "batch_maps_per_sec": B * S / (tb * 1e-3), "batch_hbm_GBps": dec_bytes / (tb * 1e-3) / 1e9,
+                      "batch_frac_of_hbm_peak": dec_bytes / (tb * 1e-3) / 1e9 / hbm_peak(), "round_trip_of_map_0_matches_rule_C_image": ok,
+                      "note": "icr_reassemble_map per map: clear + paste of all its slices; icr_reassemble_batch: all maps, hbm bytes = slices read + canvases cleared and written"}))
+    assert ok
     ws.close()
 
 
