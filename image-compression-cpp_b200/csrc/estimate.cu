@@ -71,17 +71,17 @@ __device__ __forceinline__ double size_formula(double Hbar, unsigned long long m
     return (p.overhead + (double)h) + ((double)N * b_data) / 8.0;
 }
 
-// strips per row S = 2^lg (R = 32/S rows per group) with strip width <= MAXSW, minimising warp steps
-__device__ __forceinline__ int choose_geometry(int w, int h) {
-    int lg = 5, best = 0x7fffffff;
-#pragma unroll
-    for (int l = 0; l <= 5; ++l) {
-        const int sw = (w + (1 << l) - 1) >> l;
-        const int groups = ((h << l) + 31) >> 5;
-        const int cost = groups * (20 * sw + 50 + 3 * l);      // per group: sw pixel steps (~70 instructions each) + ~180 for request, conversion, butterfly, choice
-        if (sw <= MAXSW && ((32 >> l) + 1) * (w + 2) <= TILE_CAP && cost < best) { best = cost; lg = l; }
-    }
-    return lg;
+// strips per row S = 2^lg (R = 32/S rows per group) with strip width <= MAXSW, minimising warp steps.  Lanes 0..5 cost
+// one candidate each and a warp minimum over (cost, lg) picks the cheapest, the smallest lg among equals.
+__device__ __forceinline__ int choose_geometry(int w, int h, int lane) {
+    const int l = min(lane, 5);
+    const int sw = (w + (1 << l) - 1) >> l;
+    const int groups = ((h << l) + 31) >> 5;
+    const uint32_t cost = (uint32_t)groups * (uint32_t)(20 * sw + 50 + 3 * l);    // per group: sw pixel steps (~70 instructions each) + ~180 for request, conversion, butterfly, choice
+    const bool ok = lane <= 5 && sw <= MAXSW && ((32 >> l) + 1) * (w + 2) <= TILE_CAP;
+    // groups <= 2^20 (area cap of this path) and the bracket is below 400: cost * 8 fits 32 bits
+    const uint32_t key = __reduce_min_sync(0xffffffffu, ok ? cost * 8u + (uint32_t)l : 0xffffffffu);
+    return key == 0xffffffffu ? 5 : (int)(key & 7u);
 }
 
 // The map v with seg_prefix[v] <= flat < seg_prefix[v+1], searched by the whole warp: 32 probes per round, so two
@@ -266,7 +266,7 @@ __device__ void warp_segment(const float* __restrict__ img, const LT* __restrict
     uint32_t* hist = sm.hist;
     uint32_t* tile = sm.tile;
 
-    const int lg = choose_geometry(w, h);
+    const int lg = choose_geometry(w, h, lane);
     const int S = 1 << lg, R = 32 >> lg;
     const int sr = lane >> lg, stp = lane & (S - 1);
     const int sw = (w + S - 1) >> lg;

@@ -50,7 +50,7 @@ __device__ __forceinline__ uint32_t paeth_h2(uint32_t A, uint32_t B, uint32_t C)
     __half2 pa = __habs2(da), pb = __habs2(db), pc = __habs2(dc);
     // the three-way select as exact half arithmetic on 1.0/0.0 masks: it runs on the FMA pipe, which the walk leaves
     // idle, instead of the ALU pipe the walk saturates.  bc = mb ? B : C = C + mb*(B - C); result = bc + ma*(A - bc).
-    __half2 ma = __hmul2(__hle2(pa, pb), __hle2(pa, pc));
+    __half2 ma = __hle2(pa, __hmin2(pb, pc));      // pa <= pb && pa <= pc
     __half2 mb = __hle2(pb, pc);
     __half2 bc = __hfma2(mb, da, as_h2(C));
     __half2 r = __hfma2(ma, __hsub2(as_h2(A), bc), bc);
