@@ -100,7 +100,7 @@ __device__ __forceinline__ SliceRow<LT> slice_row(const Tables& t, const unsigne
 }
 
 template <typename LT, bool SWAP>
-__global__ void __launch_bounds__(EMIT_T) slice_emit_kernel(Tables t, Inputs in, const unsigned long long* __restrict__ offsets,
+__global__ void __launch_bounds__(EMIT_T, 16) slice_emit_kernel(Tables t, Inputs in, const unsigned long long* __restrict__ offsets,
                                                              uint32_t* __restrict__ out, unsigned long long cap_px) {
     const int64_t HW = (int64_t)t.H * t.W;
     // the grid is P consecutive CTAs for each of the V maps (launch_slice_emit): CTA c strides over the segments of map c / P
@@ -167,7 +167,7 @@ cudaError_t launch_slice_plan(const Tables& t, unsigned long long* offsets, long
 cudaError_t launch_slice_emit(const Tables& t, const Inputs& in, const unsigned long long* offsets, uint8_t* out, size_t cap,
                               int swap, cudaStream_t st) {
     if (t.V <= 0) return cudaSuccess;
-    const long long resident = 148 * 12;                            // CTAs the machine holds at once (40 registers, 128 threads)
+    const long long resident = 148 * 16;                            // CTAs the machine holds at once (32 registers, 128 threads)
     const long long map_bytes = (long long)t.H * t.W * (12 + (in.label_dtype == ICR_LABELS_I64 ? 8 : 4));
     const long long in_flight = std::max(1ll, (48ll << 20) / std::max(1ll, map_bytes));      // maps that share the L2 comfortably
     long long P = std::min(1024ll, (resident + in_flight - 1) / in_flight);                  // CTAs per map
