@@ -3,8 +3,10 @@ decoder.  Only tests/ may import this; the product path never does.
 
 Pinning: the sidecar functions are checked byte for byte against tests/golden/metadata_ref.bin, which the reference's
 own src/metadata.cpp wrote (oracle/_ref/libref_metadata.so, tests/golden/make_metadata_golden.py).  The slicer and the
-decoder need OpenCV, which this image does not have, so they are restated from the source alone; the masking they do is
-the same Rule P the estimator applies, and that one is pinned through the reference's estimator outputs.
+decoder are OpenCV C++ code, which this image cannot compile; they are restated from the source and held against the
+reference's own sequence of cv:: calls made through Python cv2, the same library behind a binding
+(tests/test_slicer_vs_opencv.py: ROI + clone + copyTo(mask), split + threshold + copyTo(mask), imencode/imdecode).  The
+masking they do is the same Rule P the estimator applies, and that one is pinned through the reference's estimator outputs.
 """
 import struct
 
