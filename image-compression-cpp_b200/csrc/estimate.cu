@@ -394,7 +394,8 @@ __device__ void warp_segment(const float* __restrict__ img, const LT* __restrict
     uint4* h4 = reinterpret_cast<uint4*>(hist) + lane * 8;
     if (npx < (uint32_t)CLOG2_N) {               // no bin can lie beyond the c*log2(c) table: branch-free lookups (tab[0] = 0)
 #pragma unroll 4
-        for (int j = 0; j < 8; ++j) {
+        for (int j0 = 0; j0 < 8; ++j0) {
+            const int j = (j0 + lane) & 7;       // rotated by lane: the eight lanes of a quarter-warp are 128 B apart, unrotated they would share four banks
             const uint4 q = h4[j];
             h4[j] = make_uint4(0, 0, 0, 0);
             if (DEBUG && dbg.hist) { uint32_t* d = dbg.hist + lane * 32 + j * 4; d[0] = q.x; d[1] = q.y; d[2] = q.z; d[3] = q.w; }
@@ -402,7 +403,8 @@ __device__ void warp_segment(const float* __restrict__ img, const LT* __restrict
         }
     } else {
 #pragma unroll 1
-        for (int j = 0; j < 8; ++j) {
+        for (int j0 = 0; j0 < 8; ++j0) {
+            const int j = (j0 + lane) & 7;       // rotated by lane: the eight lanes of a quarter-warp are 128 B apart, unrotated they would share four banks
             const uint4 q = h4[j];
             h4[j] = make_uint4(0, 0, 0, 0);
             if (DEBUG && dbg.hist) { uint32_t* d = dbg.hist + lane * 32 + j * 4; d[0] = q.x; d[1] = q.y; d[2] = q.z; d[3] = q.w; }
