@@ -85,18 +85,32 @@ __device__ __forceinline__ int choose_geometry(int w, int h, int lane) {
 }
 
 // The map v with seg_prefix[v] <= flat < seg_prefix[v+1], searched by the whole warp: 32 probes per round, so two
-// dependent loads for up to 1024 maps instead of a lane's ten-step binary search.
-__device__ __forceinline__ int locate_map(const int32_t* __restrict__ sp, int V, int flat, int lane) {
+// dependent loads for up to 1024 maps instead of a lane's ten-step binary search.  seg_prefix[v] itself comes out of
+// the probes (the last probe that was <= flat, handed over by a shuffle), which saves the dependent load after the search.
+__device__ __forceinline__ int locate_map(const int32_t* __restrict__ sp, int V, int flat, int lane, int& first) {
     int lo = 0, n = V;                                  // answer in [lo, lo+n); sp[lo] <= flat
+    first = 0;                                          // sp[lo]; seg_prefix[0] = 0
     while (n > 1) {
         const int step = (n + 31) >> 5;
         const int idx = lo + (lane + 1) * step;
-        const bool le = idx < lo + n && __ldg(sp + idx) <= flat;      // monotone in lane
+        const int val = idx < lo + n ? __ldg(sp + idx) : 0x7fffffff;
+        const bool le = val <= flat;                                   // monotone in lane
         const int c = __popc(__ballot_sync(0xffffffffu, le));
+        const int hit = __shfl_sync(0xffffffffu, val, (c + 31) & 31);  // lane c-1 holds sp[lo + c*step]
+        if (c) first = hit;
         lo += c * step;
         n = min(step, n - c * step);
     }
     return lo;
+}
+
+// One request to the work list.  Plain PTX: through atomicAdd the compiler aggregates the (single-lane) atomic over the
+// warp and consumes its result with a shuffle right behind it, which makes the warp wait out the atomic's latency at
+// the top of every segment instead of at the bottom, where the result is needed.
+__device__ __forceinline__ int next_segment(int* counter) {
+    int r;
+    asm volatile("atom.global.add.s32 %0, [%1], 1;" : "=r"(r) : "l"(counter) : "memory");
+    return r;
 }
 
 // ---- stage rows yb .. yb+nr-1 of the bbox into the tile: lanes take the nr*w pixels in row-major order
@@ -445,12 +459,15 @@ __global__ void __launch_bounds__(EST_WARPS * 32, 4) estimate_kernel(Tables t, I
     // One segment per request: a warp's share of the SM makes a segment take ~15 us, so handing out several at a time left
     // warps idle for tens of microseconds at the end of the launch.  The request for the next segment is issued before
     // the current one is worked on, so its latency is hidden.
-    int flat = lane == 0 ? atomicAdd(&t.sched[1], 1) : 0;
+    int flat = 0;
+    if (lane == 0) flat = next_segment(&t.sched[1]);
     flat = __shfl_sync(0xffffffffu, flat, 0);
     while (flat < total) {
-        const int fut = lane == 0 ? atomicAdd(&t.sched[1], 1) : 0;
-        const int v = locate_map(t.seg_prefix, t.V, flat, lane);
-        const int k = flat - __ldg(t.seg_prefix + v);
+        int fut = 0;
+        if (lane == 0) fut = next_segment(&t.sched[1]);
+        int first;
+        const int v = locate_map(t.seg_prefix, t.V, flat, lane, first);
+        const int k = flat - first;
         const int64_t row = (int64_t)v * t.Kmax + k;
         const int4 bb = __ldg(t.bboxes + row);
         const LT key = (LT)__ldg(t.keys + row);
