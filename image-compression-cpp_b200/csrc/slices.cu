@@ -108,13 +108,18 @@ __global__ void __launch_bounds__(EMIT_T, 16) slice_emit_kernel(Tables t, Inputs
     {
         const int v = blockIdx.x / nsub;
         const int f0 = __ldg(t.seg_prefix + v), K = __ldg(t.seg_prefix + v + 1) - f0;      // K = 0 for a map that failed
-        if (sub >= K) return;
+        if (K <= 0) return;
+        // fewer segments than CTAs (coarse partitions, down to one whole-image segment): `parts` CTAs share a segment
+        // and interleave its pixel blocks
+        const int parts = K >= nsub ? 1 : nsub / K, kstep = K >= nsub ? nsub : K;
+        const int part = sub / kstep, k0 = sub - part * kstep;
+        if (part >= parts) return;
         const float* __restrict__ img_v = in.images + (int64_t)(v / in.S) * 3 * HW;
         const LT* __restrict__ lab_v = static_cast<const LT*>(in.labels) + (int64_t)v * HW;
-        SliceRow<LT> nx = slice_row<LT>(t, offsets, v, f0, sub);
-        for (int k = sub; k < K; k += nsub) {
+        SliceRow<LT> nx = slice_row<LT>(t, offsets, v, f0, k0);
+        for (int k = k0; k < K; k += kstep) {
             const SliceRow<LT> cur = nx;
-            if (k + nsub < K) nx = slice_row<LT>(t, offsets, v, f0, k + nsub);
+            if (k + kstep < K) nx = slice_row<LT>(t, offsets, v, f0, k + kstep);
             const int4 bb = cur.bb;
             const int w = bb.z - bb.x + 1, h = bb.w - bb.y + 1;
             if (w <= 0 || h <= 0) continue;
@@ -129,7 +134,7 @@ __global__ void __launch_bounds__(EMIT_T, 16) slice_emit_kernel(Tables t, Inputs
             const int n = w * h;                                       // the warp path's and the big kernel's bboxes are below 2^31 pixels
             const float rw = 1.0f / (float)w;
             constexpr int U = 4;
-            for (int i0 = threadIdx.x; i0 < n; i0 += EMIT_T * U) {
+            for (int i0 = threadIdx.x + part * (EMIT_T * U); i0 < n; i0 += EMIT_T * U * parts) {
                 float c0[U], c1[U], c2[U];
                 LT l[U];
 #pragma unroll
@@ -196,7 +201,12 @@ __global__ void __launch_bounds__(EMIT_T) reassemble_kernel(Tables t, int v0, in
     uint32_t* __restrict__ canvas = canvases + (int64_t)(blockIdx.x / P) * t.H * t.W;
     const int K = t.status[v] == ST_OK ? t.K[v] : 0;
     const int f0 = t.seg_prefix[v];
-    for (int k = blockIdx.x % P; k < K; k += P) {
+    if (K <= 0) return;
+    const int sub = blockIdx.x % P;
+    const int parts = K >= P ? 1 : P / K, kstep = K >= P ? P : K;          // CTAs that share a slice when there are few, as in the emit
+    const int part = sub / kstep;
+    if (part >= parts) return;
+    for (int k = sub - part * kstep; k < K; k += kstep) {
         const int4 bb = t.bboxes[(int64_t)v * t.Kmax + k];
         const int w = bb.z - bb.x + 1, h = bb.w - bb.y + 1;
         if (w <= 0 || h <= 0) continue;
@@ -207,7 +217,7 @@ __global__ void __launch_bounds__(EMIT_T) reassemble_kernel(Tables t, int v0, in
         const int n = w * h;
         const float rw = 1.0f / (float)w;
         constexpr int U = 4;
-        for (int i0 = threadIdx.x; i0 < n; i0 += EMIT_T * U) {
+        for (int i0 = threadIdx.x + part * (EMIT_T * U); i0 < n; i0 += EMIT_T * U * parts) {
             uint32_t px[U];
 #pragma unroll
             for (int u = 0; u < U; ++u) {

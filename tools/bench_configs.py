@@ -148,6 +148,9 @@ def main():
     if "3" in which:
         im, lab, sz = synth.make_batch(3, B=32)
         run("cfg3: 256 x 512x512, Voronoi (SLIC-style) ~1024 segments", im, lab, sz, 8)
+    if "big" in which:          # adversarial for the warp path: every map is ONE whole-image segment (Rule M, chunk = 4), all through big_kernel
+        im, lab, sz = synth.make_batch(2)
+        run("big: 512 x 224x224, one whole-image segment per map", im, np.zeros_like(lab), sz, 8)
     if "4" in which:
         im, lab, sz = synth.make_multi_batch(B=32, S=8)
         run("cfg4: 256 x 224x224, 8 label maps per image (rectangles / region growing)", im, lab, sz, 8)
