@@ -181,7 +181,7 @@ def run_reference(args):
                     cpu_baseline={"value": v, "unit": "images/sec", "cores": 1, "kind": "port",
                                   "sample": f"{n} images per step, scalar C restatement (oracle/reward_oracle.c); oracle/_ref not available"})
     line["e2e"] = {"value": line["value"], "unit": "images/sec", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
-    print(json.dumps(line))
+    print(json.dumps(line), file=args.out, flush=True)
 
 
 # --------------------------------------------------------------------------------------------
@@ -194,6 +194,12 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
+    # stdout carries exactly one JSON line: whatever libraries write to file descriptor 1 on the way (NCCL prints its
+    # version banner there when NCCL_DEBUG is set) goes to stderr instead, and the line is written to the real stdout.
+    sys.stdout.flush()
+    real_stdout = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    args.out = real_stdout
     if args.impl == "reference":
         return run_reference(args)
 
@@ -390,7 +396,7 @@ def main():
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(images, labels, n_images=POOL)
     if rank == 0:
-        print(json.dumps(line))
+        print(json.dumps(line), file=args.out, flush=True)
     if world > 1:
         dist.destroy_process_group()
 

@@ -38,11 +38,12 @@ def run(name, images, labels, sizes, pool_reps, steps=10):
     K = [len(np.unique(l)) for l in labels.reshape(-1, H, W)[:32]]
     ws = reward.Workspace(dev, B * S, H, W, Kmax=2048)
     prm = reward.make_params()
+    code = 1 if labels.dtype == np.int64 else 0                   # ICR_LABELS_I64 / ICR_LABELS_I32
     out = torch.empty(B * S, dtype=torch.float64, device=dev)
     st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
 
     def step():
-        rc = L.icr_compute_rewards(C.c_void_p(ti.data_ptr()), C.c_void_p(tl.data_ptr()), 0, C.c_void_p(ts.data_ptr()), B, S, H, W,
+        rc = L.icr_compute_rewards(C.c_void_p(ti.data_ptr()), C.c_void_p(tl.data_ptr()), code, C.c_void_p(ts.data_ptr()), B, S, H, W,
                                    C.byref(prm), C.c_void_p(out.data_ptr()), ws.handle, st)
         assert rc == 0, L.icr_last_error()
     for _ in range(3):
@@ -69,7 +70,7 @@ def run(name, images, labels, sizes, pool_reps, steps=10):
         want = orc.compute_rewards(images[:n], labels[:n], sizes[:n])
     got = out.cpu().numpy()[:want.size]
     err = float(np.max(np.abs(got - want) / np.abs(want)))
-    px_bytes = 12 + 4 * S
+    px_bytes = 12 + labels.dtype.itemsize * S
     alg = B * (H * W * px_bytes + S * (np.mean(K) * 28 + 16))
     print(json.dumps({"config": name, "images": B, "label_maps": B * S, "H": H, "W": W, "mean_K": float(np.mean(K)),
                       "ms_per_step_kernels": ms, "images_per_sec": B / (ms * 1e-3), "rewards_per_sec": B * S / (ms * 1e-3),
@@ -148,6 +149,9 @@ def main():
     if "3" in which:
         im, lab, sz = synth.make_batch(3, B=32)
         run("cfg3: 256 x 512x512, Voronoi (SLIC-style) ~1024 segments", im, lab, sz, 8)
+    if "i64" in which:          # the bench workload (512 of config 5) with int64 labels: what compute_rewards_batched's own callers hold
+        im, lab, sz = synth.make_batch(5, B=64)
+        run("i64: 512 x 224x224, BSP rectangles, int64 labels", im, lab.astype(np.int64), sz, 8)
     if "big" in which:          # adversarial for the warp path: every map is ONE whole-image segment (Rule M, chunk = 4), all through big_kernel
         im, lab, sz = synth.make_batch(2)
         run("big: 512 x 224x224, one whole-image segment per map", im, np.zeros_like(lab), sz, 8)
