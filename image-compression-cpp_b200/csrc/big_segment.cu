@@ -72,16 +72,16 @@ __device__ void block_segment(const Src& src, int x0, int y0, int w, int h, int 
         int f = 4;
         if (p.adaptive) {
             Costs5 c = {0, 0, 0, 0, 0};
+            uint32_t last_cur = 0u, last_up = 0u;        // lane 31's pixels of the step before: lane 0's neighbours (zero left of the bbox)
 #pragma unroll 2
             for (int xb = 0; xb < w; xb += 32) {         // the lane to the left holds this pixel's left and upper-left neighbours
                 const int x = xb + lane;
                 const uint32_t cur = x < w ? src.px(y0 + y, x0 + x) : 0u;
                 const uint32_t up = (x < w && y > 0) ? src.px(y0 + y - 1, x0 + x) : 0u;
                 uint32_t left = __shfl_up_sync(0xffffffffu, cur, 1), ul = __shfl_up_sync(0xffffffffu, up, 1);
-                if (lane == 0) {
-                    left = xb > 0 ? src.px(y0 + y, x0 + xb - 1) : 0u;
-                    ul = (xb > 0 && y > 0) ? src.px(y0 + y - 1, x0 + xb - 1) : 0u;
-                }
+                if (lane == 0) { left = last_cur; ul = last_up; }
+                last_cur = __shfl_sync(0xffffffffu, cur, 31);
+                last_up = __shfl_sync(0xffffffffu, up, 31);
                 if (x < w) add_costs(c, cur, left, up, ul);
             }
             for (int o = 16; o; o >>= 1) {
@@ -113,8 +113,13 @@ __device__ void block_segment(const Src& src, int x0, int y0, int w, int h, int 
         const uint32_t tile_px = ck * ((uint32_t)BIG_TILE_PX / ck);               // tile bytes = tile_px * C: chunks * C whole chunks
         for (uint32_t p0 = 0; p0 < n_px; p0 += tile_px) {
             const uint32_t here = min(tile_px, n_px - p0);
+            // every warp takes a contiguous run of the tile's pixels, 32 per step, so that lane 0's neighbours are lane 31's
+            // pixels of the step before; only a warp's first step fetches them
+            const uint32_t span = (((here + BIG_T / 32 - 1) / (BIG_T / 32)) + 31u) & ~31u;
+            const uint32_t wbeg = (uint32_t)warp * span, wend = min(wbeg + span, here);
+            uint32_t last_cur = 0u, last_up = 0u;
 #pragma unroll 2
-            for (uint32_t base = (uint32_t)(tid - lane); base < here; base += BIG_T) {
+            for (uint32_t base = wbeg; base < wend; base += 32) {
                 const uint32_t q = base + lane;
                 const bool in = q < here;
                 const uint32_t pi = p0 + (in ? q : 0u);
@@ -122,10 +127,15 @@ __device__ void block_segment(const Src& src, int x0, int y0, int w, int h, int 
                 const uint32_t cur = in ? src.px(y0 + y, x0 + x) : 0u;
                 const uint32_t up = (in && y > 0) ? src.px(y0 + y - 1, x0 + x) : 0u;
                 uint32_t left = __shfl_up_sync(0xffffffffu, cur, 1), ul = __shfl_up_sync(0xffffffffu, up, 1);
-                if (lane == 0 && in && x > 0) {
-                    left = src.px(y0 + y, x0 + x - 1);
-                    ul = y > 0 ? src.px(y0 + y - 1, x0 + x - 1) : 0u;
+                if (lane == 0) {
+                    if (base != wbeg) { left = last_cur; ul = last_up; }
+                    else if (in && x > 0) {
+                        left = src.px(y0 + y, x0 + x - 1);
+                        ul = y > 0 ? src.px(y0 + y - 1, x0 + x - 1) : 0u;
+                    }
                 }
+                last_cur = __shfl_sync(0xffffffffu, cur, 31);
+                last_up = __shfl_sync(0xffffffffu, up, 31);
                 if (x == 0) { left = 0u; ul = 0u; }
                 if (in) {
                     const uint32_t r4 = residual4(filt[y], cur, left, up, ul);
