@@ -14,6 +14,8 @@ namespace icr {
 
 constexpr int BIG_T = 256;
 constexpr int BIG_TILE_PX = 4096;       // residual words kept in shared memory per tile of the stream
+constexpr int BAND_MAX_W = 1024;        // widest bbox of the banded path (its halo row lives in shared memory)
+constexpr int BAND_MAX_R = 256;         // most rows of a band
 
 struct BigDebug { uint32_t* row_costs; uint8_t* filter_id; uint32_t* hist; unsigned long long* match; double* size; };
 
@@ -67,6 +69,115 @@ __device__ void block_segment(const Src& src, int x0, int y0, int w, int h, int 
     for (int i = tid; i < 4 * 256; i += BIG_T) s_hist[i] = 0;
     if (tid == 0) { s_ms = 0; s_mc = 0; s_mls = 0; }
 
+    const unsigned long long N = (unsigned long long)w * h * C;
+    const unsigned long long chunk = (N + 65535ull) / 65536ull;
+    const unsigned long long nchunks = (N + chunk - 1) / chunk;
+    unsigned long long ms = 0, mc = 0;
+
+    // ---- banded path (RGBA, chunks of whole pixels, bbox no wider than BAND_MAX_W): the masked pixels of a band of rows are
+    // fetched ONCE into shared memory and serve the filter choice and the residuals of the band; a band is a whole number
+    // of reference chunks, so no chunk straddles two bands.  The general path below reads every pixel four times.
+    int R = 0;
+    if (C == 4 && (chunk & 3ull) == 0 && w <= BAND_MAX_W && chunk <= (unsigned long long)BIG_TILE_PX) {
+        const int wpc = (int)(chunk >> 2);                     // pixels per chunk
+        int a = w, b = wpc;
+        while (b) { const int t = a % b; a = b; b = t; }       // gcd(w, wpc)
+        const int g = wpc / a;                                 // rows per band must be a multiple of g
+        R = min(min(h, BIG_TILE_PX / w), BAND_MAX_R);
+        if (R < h) R = (R / g) * g;                            // the last band may end anywhere: it ends the stream
+    }
+    if (R > 0) {
+        __shared__ uint32_t s_pix[BIG_TILE_PX];
+        __shared__ uint32_t s_halo[BAND_MAX_W];
+        __shared__ uint8_t s_filt[BAND_MAX_R];
+        const float rw = 1.0f / (float)w;
+        const uint32_t wpc = (uint32_t)(chunk >> 2);
+        for (int yb = 0; yb < h; yb += R) {
+            const int nr = min(R, h - yb);
+            const int here = nr * w;
+            // the row above the band: zeros above the bbox, else the last row of the band before (always a full band)
+            for (int x = tid; x < w; x += BIG_T) s_halo[x] = yb ? s_pix[(R - 1) * w + x] : 0u;
+            __syncthreads();
+#pragma unroll 4
+            for (int q = tid; q < here; q += BIG_T) {
+                int y = __float2int_rz(((float)q + 0.5f) * rw);
+                y += (y + 1) * w <= q;
+                y -= y * w > q;
+                s_pix[q] = src.px(y0 + yb + y, x0 + (q - y * w));
+            }
+            __syncthreads();
+            // filter per row (Rule F): a warp per row, left neighbours by shuffle, lane 31's pixels carried to the next step
+            for (int r = warp; r < nr; r += BIG_T / 32) {
+                int f = 4;
+                if (p.adaptive) {
+                    Costs5 c = {0, 0, 0, 0, 0};
+                    const uint32_t* cr = s_pix + r * w;
+                    const uint32_t* ur = r ? cr - w : s_halo;
+                    uint32_t last_cur = 0u, last_up = 0u;
+                    for (int xb = 0; xb < w; xb += 32) {
+                        const int x = xb + lane;
+                        const uint32_t cur = x < w ? cr[x] : 0u, up = x < w ? ur[x] : 0u;
+                        uint32_t left = __shfl_up_sync(0xffffffffu, cur, 1), ul = __shfl_up_sync(0xffffffffu, up, 1);
+                        if (lane == 0) { left = last_cur; ul = last_up; }
+                        last_cur = __shfl_sync(0xffffffffu, cur, 31);
+                        last_up = __shfl_sync(0xffffffffu, up, 31);
+                        if (x < w) add_costs(c, cur, left, up, ul);
+                    }
+                    for (int o = 16; o; o >>= 1) {
+                        c.none += __shfl_xor_sync(0xffffffffu, c.none, o);
+                        c.sub += __shfl_xor_sync(0xffffffffu, c.sub, o);
+                        c.up += __shfl_xor_sync(0xffffffffu, c.up, o);
+                        c.avg += __shfl_xor_sync(0xffffffffu, c.avg, o);
+                        c.paeth += __shfl_xor_sync(0xffffffffu, c.paeth, o);
+                    }
+                    f = pick_filter(c);
+                    if (lane == 0 && dbg.row_costs) {
+                        uint32_t* rc = dbg.row_costs + 5 * (int64_t)(yb + r);
+                        rc[0] = c.none; rc[1] = c.sub; rc[2] = c.up; rc[3] = c.avg; rc[4] = c.paeth;
+                    }
+                }
+                if (lane == 0) { s_filt[r] = (uint8_t)f; if (dbg.filter_id) dbg.filter_id[yb + r] = (uint8_t)f; }
+            }
+            __syncthreads();
+            // residuals of the band in stream order (Rules R, H)
+            for (int q = tid; q < here; q += BIG_T) {
+                int y = __float2int_rz(((float)q + 0.5f) * rw);
+                y += (y + 1) * w <= q;
+                y -= y * w > q;
+                const int x = q - y * w;
+                const uint32_t cur = s_pix[q];
+                const uint32_t up = y ? s_pix[q - w] : s_halo[x];
+                const uint32_t left = x ? s_pix[q - 1] : 0u;
+                const uint32_t ul = x ? (y ? s_pix[q - w - 1] : s_halo[x - 1]) : 0u;
+                const uint32_t r4 = residual4(s_filt[y], cur, left, up, ul);
+                s_tile[q] = r4;
+                atomicAdd(&s_hist[r4 & 255u], 1u);
+                atomicAdd(&s_hist[256 + ((r4 >> 8) & 255u)], 1u);
+                atomicAdd(&s_hist[512 + ((r4 >> 16) & 255u)], 1u);
+                atomicAdd(&s_hist[768 + (r4 >> 24)], 1u);
+            }
+            __syncthreads();
+            // run statistics (Rule M): a thread per reference chunk of wpc whole pixels
+            for (uint32_t w0 = (uint32_t)tid * wpc; w0 < (uint32_t)here; w0 += BIG_T * wpc) {
+                const uint32_t w1 = min(w0 + wpc, (uint32_t)here);
+                int prev = -1, run = 0;
+                for (uint32_t wi = w0; wi < w1; ++wi) {
+                    const uint32_t r4 = s_tile[wi];
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) {
+                        const int bv = (int)((r4 >> (8 * c)) & 255u);
+                        if (bv == prev) { ++run; }
+                        else {
+                            if (prev >= 0 && run >= p.L_min) { ms += (unsigned long long)run; mc += 1; }
+                            prev = bv; run = 1;
+                        }
+                    }
+                }
+                if (run >= p.L_min) { ms += (unsigned long long)run; mc += 1; }
+            }
+            __syncthreads();
+        }
+    } else {
     // ---- phase 1: filter per row (Rule F)
     for (int y = warp; y < h; y += BIG_T / 32) {
         int f = 4;
@@ -104,10 +215,6 @@ __device__ void block_segment(const Src& src, int x0, int y0, int w, int h, int 
     // ---- phase 2: the filtered stream, tile by tile (Rules R, H, M).  A tile is a whole number of reference chunks and of
     // pixels.  Step A: a lane per pixel in stream order -- coalesced loads, left neighbours by shuffle -- leaves the pixel's
     // residual bytes in shared memory and feeds the histogram.  Step B: a thread per reference chunk walks its bytes there.
-    const unsigned long long N = (unsigned long long)w * h * C;
-    const unsigned long long chunk = (N + 65535ull) / 65536ull;
-    const unsigned long long nchunks = (N + chunk - 1) / chunk;
-    unsigned long long ms = 0, mc = 0;
     if (chunk <= (unsigned long long)BIG_TILE_PX) {
         const uint32_t n_px = (uint32_t)w * (uint32_t)h, ck = (uint32_t)chunk;
         const uint32_t tile_px = ck * ((uint32_t)BIG_TILE_PX / ck);               // tile bytes = tile_px * C: chunks * C whole chunks
@@ -216,6 +323,7 @@ __device__ void block_segment(const Src& src, int x0, int y0, int w, int h, int 
             if (run >= p.L_min) { ms += (unsigned long long)run; mc += 1; }
         }
     }
+    }   // general path
     if (ms) { atomicAdd(&s_ms, ms); atomicAdd(&s_mls, ms); }    // match_symbols == match_len_sum (:440-442)
     if (mc) atomicAdd(&s_mc, mc);
     __syncthreads();
@@ -252,7 +360,7 @@ __device__ __forceinline__ bool flagged(int4 bb, int L_min) { return for_big_ker
 // their reward up front.  Maps that do hold such segments split them over BIG_CTAS parts; the part that finishes last
 // computes the reward, every segment size of the map being final then.
 template <typename LT>
-__global__ void __launch_bounds__(BIG_T) big_kernel(Tables t, Inputs in, EstParams p, const double* __restrict__ image_sizes,
+__global__ void __launch_bounds__(BIG_T, 4) big_kernel(Tables t, Inputs in, EstParams p, const double* __restrict__ image_sizes,
                                                     double* __restrict__ rewards) {
     __shared__ int s_last;
     const int64_t HW = (int64_t)t.H * t.W;
