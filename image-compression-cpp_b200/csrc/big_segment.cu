@@ -90,7 +90,6 @@ __device__ void block_segment(const Src& src, int x0, int y0, int w, int h, int 
         __shared__ uint32_t s_pix[BIG_TILE_PX];
         __shared__ uint32_t s_halo[BAND_MAX_W];
         __shared__ uint8_t s_filt[BAND_MAX_R];
-        const float rw = 1.0f / (float)w;
         const uint32_t wpc = (uint32_t)(chunk >> 2);
         for (int yb = 0; yb < h; yb += R) {
             const int nr = min(R, h - yb);
@@ -98,12 +97,11 @@ __device__ void block_segment(const Src& src, int x0, int y0, int w, int h, int 
             // the row above the band: zeros above the bbox, else the last row of the band before (always a full band)
             for (int x = tid; x < w; x += BIG_T) s_halo[x] = yb ? s_pix[(R - 1) * w + x] : 0u;
             __syncthreads();
+            // a warp per row, lanes along x (these bboxes are wide: no row/column split per pixel)
+            for (int r = warp; r < nr; r += BIG_T / 32) {
+                uint32_t* dst = s_pix + r * w;
 #pragma unroll 4
-            for (int q = tid; q < here; q += BIG_T) {
-                int y = __float2int_rz(((float)q + 0.5f) * rw);
-                y += (y + 1) * w <= q;
-                y -= y * w > q;
-                s_pix[q] = src.px(y0 + yb + y, x0 + (q - y * w));
+                for (int x = lane; x < w; x += 32) dst[x] = src.px(y0 + yb + r, x0 + x);
             }
             __syncthreads();
             // filter per row (Rule F): a warp per row, left neighbours by shuffle, lane 31's pixels carried to the next step
@@ -140,24 +138,40 @@ __device__ void block_segment(const Src& src, int x0, int y0, int w, int h, int 
             }
             __syncthreads();
             // residuals of the band in stream order (Rules R, H)
-            for (int q = tid; q < here; q += BIG_T) {
-                int y = __float2int_rz(((float)q + 0.5f) * rw);
-                y += (y + 1) * w <= q;
-                y -= y * w > q;
-                const int x = q - y * w;
-                const uint32_t cur = s_pix[q];
-                const uint32_t up = y ? s_pix[q - w] : s_halo[x];
-                const uint32_t left = x ? s_pix[q - 1] : 0u;
-                const uint32_t ul = x ? (y ? s_pix[q - w - 1] : s_halo[x - 1]) : 0u;
-                const uint32_t r4 = residual4(s_filt[y], cur, left, up, ul);
-                s_tile[q] = r4;
-                atomicAdd(&s_hist[r4 & 255u], 1u);
-                atomicAdd(&s_hist[256 + ((r4 >> 8) & 255u)], 1u);
-                atomicAdd(&s_hist[512 + ((r4 >> 16) & 255u)], 1u);
-                atomicAdd(&s_hist[768 + (r4 >> 24)], 1u);
+            for (int r = warp; r < nr; r += BIG_T / 32) {
+                const uint32_t* cr = s_pix + r * w;
+                const uint32_t* ur = r ? cr - w : s_halo;
+                uint32_t* rr = s_tile + r * w;
+                const int f = s_filt[r];
+                for (int x = lane; x < w; x += 32) {
+                    const uint32_t cur = cr[x], up = ur[x];
+                    const uint32_t left = x ? cr[x - 1] : 0u, ul = x ? ur[x - 1] : 0u;
+                    const uint32_t r4 = residual4(f, cur, left, up, ul);
+                    rr[x] = r4;
+                    atomicAdd(&s_hist[r4 & 255u], 1u);
+                    atomicAdd(&s_hist[256 + ((r4 >> 8) & 255u)], 1u);
+                    atomicAdd(&s_hist[512 + ((r4 >> 16) & 255u)], 1u);
+                    atomicAdd(&s_hist[768 + (r4 >> 24)], 1u);
+                }
             }
             __syncthreads();
-            // run statistics (Rule M): a thread per reference chunk of wpc whole pixels
+            // run statistics (Rule M): a thread per reference chunk of wpc whole pixels.  A chunk of one pixel (every bbox up
+            // to 65536 pixels) is four bytes: its runs follow from the three neighbour comparisons without a loop.
+            if (wpc == 1) {
+                const int Lm = p.L_min;
+                for (int q = tid; q < here; q += BIG_T) {
+                    const uint32_t r4 = s_tile[q];
+                    const uint32_t eq = (r4 ^ (r4 >> 8));                  // byte c of eq is zero when bytes c and c+1 are equal
+                    const bool e1 = (eq & 0xffu) == 0, e2 = (eq & 0xff00u) == 0, e3 = (eq & 0xff0000u) == 0;
+                    // run lengths of the 4-byte string, left to right
+                    int run = 1, m = 0, n = 0;
+                    if (e1) ++run; else { if (run >= Lm) { m += run; ++n; } run = 1; }
+                    if (e2) ++run; else { if (run >= Lm) { m += run; ++n; } run = 1; }
+                    if (e3) ++run; else { if (run >= Lm) { m += run; ++n; } run = 1; }
+                    if (run >= Lm) { m += run; ++n; }
+                    ms += (unsigned long long)m; mc += (unsigned long long)n;
+                }
+            } else
             for (uint32_t w0 = (uint32_t)tid * wpc; w0 < (uint32_t)here; w0 += BIG_T * wpc) {
                 const uint32_t w1 = min(w0 + wpc, (uint32_t)here);
                 int prev = -1, run = 0;
