@@ -184,6 +184,30 @@ def run_reference(args):
     print(json.dumps(line), file=args.out, flush=True)
 
 
+def bind_to_gpu_numa_node(local):
+    """One process per GPU: run on the cores of the NUMA node the GPU hangs off, so that the pinned host buffers of the
+    host-buffer entry are first touched in that node's memory and the H2D copies do not cross the socket link.
+    Best effort (sysfs + sched_setaffinity); returns the node or None."""
+    try:
+        import torch
+        p = torch.cuda.get_device_properties(local)
+        bdf = "%04x:%02x:%02x.0" % (p.pci_domain_id, p.pci_bus_id, p.pci_device_id)
+        node = int(open(f"/sys/bus/pci/devices/{bdf}/numa_node").read())
+        if node < 0:
+            return None
+        cpus = set()
+        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return node
+    except Exception:
+        pass
+    return None
+
+
 # --------------------------------------------------------------------------------------------
 def main():
     ap = argparse.ArgumentParser()
@@ -210,6 +234,7 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    numa = bind_to_gpu_numa_node(local)
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
@@ -383,7 +408,7 @@ def main():
                    "parallelism": f"dp{world}: images sharded, rewards exchanged by {exchange}, EMA on the gathered vector" if world > 1 else "single GPU"},
         "e2e": {"value": e2e_value, "unit": "images/sec", "h2d_bytes_per_step": int(images.nbytes + labels.nbytes + sizes.nbytes),
                 "d2h_bytes_per_step": int(pr.numel() * 8), "ms_per_step": e2e_ms / e2e_steps, "steps": e2e_steps,
-                "h2d_copy_alone_ms": copy_ms,
+                "h2d_copy_alone_ms": copy_ms, "numa_node": numa,
                 "api": "icr_compute_rewards_host (C ABI, pinned host buffers; the batch is copied in four pieces on a second stream "
                        "under the kernels of the piece before)"},
         "gpu_launches": launches,
