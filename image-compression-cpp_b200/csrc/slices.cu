@@ -10,7 +10,7 @@
 namespace icr {
 
 constexpr int PLAN_T = 1024;
-constexpr int EMIT_T = 128;
+constexpr int EMIT_T = 64;
 
 // ---- plan: offsets[f] = byte offset of the slice of flat segment f = seg_prefix[v] + k, in (v, k) order;
 // summary = {segments, total bytes}.  Three small launches: bytes per map (a warp per map), a scan over the maps
@@ -100,7 +100,7 @@ __device__ __forceinline__ SliceRow<LT> slice_row(const Tables& t, const unsigne
 }
 
 template <typename LT, bool SWAP>
-__global__ void __launch_bounds__(EMIT_T, 16) slice_emit_kernel(Tables t, Inputs in, const unsigned long long* __restrict__ offsets,
+__global__ void __launch_bounds__(EMIT_T, 32) slice_emit_kernel(Tables t, Inputs in, const unsigned long long* __restrict__ offsets,
                                                              uint32_t* __restrict__ out, unsigned long long cap_px) {
     const int64_t HW = (int64_t)t.H * t.W;
     // the grid is P consecutive CTAs for each of the V maps (launch_slice_emit): CTA c strides over the segments of map c / P
@@ -172,7 +172,7 @@ cudaError_t launch_slice_plan(const Tables& t, unsigned long long* offsets, long
 cudaError_t launch_slice_emit(const Tables& t, const Inputs& in, const unsigned long long* offsets, uint8_t* out, size_t cap,
                               int swap, cudaStream_t st) {
     if (t.V <= 0) return cudaSuccess;
-    const long long resident = 148 * 16;                            // CTAs the machine holds at once (32 registers, 128 threads)
+    const long long resident = 148 * 32;                            // CTAs the machine holds at once (32 registers, 64 threads)
     const long long map_bytes = (long long)t.H * t.W * (12 + (in.label_dtype == ICR_LABELS_I64 ? 8 : 4));
     const long long in_flight = std::max(1ll, (48ll << 20) / std::max(1ll, map_bytes));      // maps that share the L2 comfortably
     long long P = std::min(1024ll, (resident + in_flight - 1) / in_flight);                  // CTAs per map
@@ -256,7 +256,7 @@ cudaError_t launch_reassemble(const Tables& t, int v0, int nmaps, const unsigned
     cudaError_t e = cudaMemsetAsync(canvases, 0, map_bytes * (size_t)nmaps, st);   // cv::Scalar(0,0,0,0), :50
     if (e != cudaSuccess) return e;
     // CTAs per map: enough that the maps in flight (canvas + slices, ~2.5x the canvas) share the L2, see launch_slice_emit
-    const long long resident = 148 * 16;
+    const long long resident = 148 * 32;
     const long long in_flight = std::max(1ll, (48ll << 20) / std::max<long long>(1, (long long)map_bytes * 5 / 2));
     long long P = std::min(1024ll, (resident + in_flight - 1) / in_flight);
     if (nmaps == 1) P = 148 * 4;
