@@ -138,11 +138,11 @@ def run_reference(args):
         return
     import torch
     images, labels, sizes = make_shard(0)
-    n = 32                                                       # bounded sample per step (the reference issues ~900 stream ops per image)
+    n = PER_GPU                                                  # the same 512 images per step as the b200 arm (about 1.7 s per step: ~900 stream ops per image)
     path = os.path.join(ROOT, "oracle", "_ref", "libref_reward.so")
     line = {"impl": "reference", "metric": METRIC, "unit": "images/sec", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": {"workload": f"cfg5 shard sample: {n} of 512 x 224x224 RGB, BSP-rectangle labels", "per_gpu_batch": n}}
+            "config": {"workload": "cfg5 shard: 512 x 224x224 RGB f32 planes per GPU, BSP-rectangle int32 label maps (labels 7*id+3)", "per_gpu_batch": n, "global_batch": n}}
     if os.path.exists(path) and torch.cuda.is_available():
         L = C.CDLL(path)
         L.ref_last_error.restype = C.c_char_p
@@ -386,7 +386,7 @@ def main():
         L.icr_profile_read(ws.handle, kms[i].ctypes.data_as(C.c_void_p))
     L.icr_workspace_set_profile(ws.handle, 0)
     kavg = kms.mean(0).astype(np.float64)
-    names = ["prep_kernel", "estimate_kernel", "big_kernel", "reward_kernel"]
+    names = ["prep_kernel", "narrow_kernel", "estimate_kernel (wide)", "big_kernel"]
     top = int(np.argmax(kavg))
     peak, peak_src = peaks()
     alg_bytes = bytes_per_image(Kmean) * B

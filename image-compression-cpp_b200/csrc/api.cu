@@ -22,6 +22,8 @@ struct icr_workspace {
     cudaEvent_t copy_ev[HOST_CHUNKS + 1];
     int profile;           // record events between the kernels of icr_compute_rewards
     cudaEvent_t ev[5];
+    int dirty;             // a batch call failed between prep and the tail kernel: the work lists must be reset by hand
+    int prefix_valid;      // seg_prefix matches the tables (built on demand for the slice entries)
 };
 
 namespace icr {
@@ -38,7 +40,19 @@ static int cuda_fail(cudaError_t e, const char* what) {
 
 static size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
 
-struct Layout { size_t K, status, counts, bboxes, keys, sizes, err, seg_prefix, sched, big_filter, clog2, runs, slice_map_off, map_max, big_done, total; };
+int sm_count() {
+    static int cached[64] = {0};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev >= 0 && dev < 64 && cached[dev]) return cached[dev];
+    int n = 148;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n < 1) n = 148;
+    if (dev >= 0 && dev < 64) cached[dev] = n;
+    return n;
+}
+
+struct Layout { size_t K, status, counts, bboxes, keys, sizes, err, seg_prefix, sched, big_filter, clog2, heads, hslot, chg, slice_map_off,
+                done, list_narrow, list_other, total; };
 
 static Layout layout(int V, int H, int W, int Kmax) {
     Layout l; size_t o = 0;
@@ -50,13 +64,16 @@ static Layout layout(int V, int H, int W, int Kmax) {
     l.sizes = o; o = align_up(o + (size_t)V * Kmax * 8);
     l.err = o; o = align_up(o + 16);
     l.seg_prefix = o; o = align_up(o + ((size_t)V + 1) * 4);
-    l.sched = o; o = align_up(o + 16);
-    l.big_filter = o; o = align_up(o + (size_t)V * BIG_CTAS * H);
+    l.sched = o; o = align_up(o + (size_t)SCHED_N * 4);
+    l.big_filter = o; o = align_up(o + (size_t)BIG_GRID_MAX * H);
     l.clog2 = o; o = align_up(o + (size_t)CLOG2_N * 8);
-    l.runs = o; o = align_up(o + (size_t)V * run_capacity(H, W) * 8);
+    l.heads = o; o = align_up(o + (size_t)V * head_capacity(H, W) * 4);
+    l.hslot = o; o = align_up(o + (size_t)V * head_capacity(H, W) * 4);
+    l.chg = o; o = align_up(o + (chg_in_smem(H, W) ? 0 : (size_t)V * (size_t)chg_bytes(H, W)));
     l.slice_map_off = o; o = align_up(o + (size_t)V * 8);
-    l.map_max = o; o = align_up(o + (size_t)V * 8);
-    l.big_done = o; o = align_up(o + (size_t)V * 4);
+    l.done = o; o = align_up(o + (size_t)V * 4);
+    l.list_narrow = o; o = align_up(o + (size_t)V * Kmax * 8);
+    l.list_other = o; o = align_up(o + (size_t)V * Kmax * 8);
     l.total = o;
     return l;
 }
@@ -108,6 +125,8 @@ int icr_workspace_create(icr_workspace** out, int device, int V, int H, int W, i
     if (V <= 0 || H <= 0 || W <= 0 || Kmax <= 0) return fail(ICR_EINVAL, "V, H, W and Kmax must be positive");
     if ((int64_t)H * W >= (1ll << 31))
         return fail(ICR_ECAPACITY, "label maps of 2^31 pixels and more are not supported (32-bit pixel offsets inside a map)");
+    if ((int64_t)V * (Kmax < (int64_t)H * W ? Kmax : (int64_t)H * W) >= (1ll << 31))
+        return fail(ICR_ECAPACITY, "V * Kmax must stay below 2^31 (32-bit positions in the work lists)");
     if ((int64_t)Kmax > (int64_t)H * W) Kmax = H * W;
     ICR_CUDA(cudaSetDevice(device), "cudaSetDevice");
     icr_workspace* ws = new icr_workspace();
@@ -123,9 +142,12 @@ int icr_workspace_create(icr_workspace** out, int device, int V, int H, int W, i
     t.counts = (int32_t*)(ws->base + l.counts); t.bboxes = (int4*)(ws->base + l.bboxes); t.seg_sizes = (double*)(ws->base + l.sizes);
     t.err = (int32_t*)(ws->base + l.err); t.big_filter = (uint8_t*)(ws->base + l.big_filter); t.clog2 = (const double*)(ws->base + l.clog2);
     t.V = V; t.H = H; t.W = W; t.Kmax = Kmax;
-    t.runs = (uint2*)(ws->base + l.runs); t.run_cap = run_capacity(H, W);
+    t.heads = (uint32_t*)(ws->base + l.heads); t.hslot = (uint32_t*)(ws->base + l.hslot); t.head_cap = head_capacity(H, W);
+    t.chg_global = chg_in_smem(H, W) ? nullptr : (uint8_t*)(ws->base + l.chg); t.chg_stride = chg_bytes(H, W);
     t.slice_map_off = (unsigned long long*)(ws->base + l.slice_map_off);
-    t.map_max = (int2*)(ws->base + l.map_max); t.big_done = (int32_t*)(ws->base + l.big_done);
+    t.done = (int32_t*)(ws->base + l.done);
+    t.list_narrow = (uint2*)(ws->base + l.list_narrow); t.list_other = (uint2*)(ws->base + l.list_other);
+    t.list_cap = (int64_t)V * Kmax;
     std::vector<double> tab(CLOG2_N);
     tab[0] = 0.0;
     for (int c = 1; c < CLOG2_N; ++c) tab[c] = (double)c * std::log2((double)c);
@@ -134,9 +156,8 @@ int icr_workspace_create(icr_workspace** out, int device, int V, int H, int W, i
     if (e == cudaSuccess) e = cudaMemset(ws->base + l.status, 0, (size_t)V * 4);
     if (e == cudaSuccess) e = cudaMemset(ws->base + l.err, 0, 16);
     if (e == cudaSuccess) e = cudaMemset(ws->base + l.seg_prefix, 0, ((size_t)V + 1) * 4);
-    if (e == cudaSuccess) e = cudaMemset(ws->base + l.sched, 0, 16);
-    if (e == cudaSuccess) e = cudaMemset(ws->base + l.big_done, 0, (size_t)V * 4);
-    if (e == cudaSuccess) e = cudaMemset(ws->base + l.map_max, 0x7f, (size_t)V * 8);
+    if (e == cudaSuccess) e = cudaMemset(ws->base + l.sched, 0, (size_t)SCHED_N * 4);
+    if (e == cudaSuccess) e = cudaMemset(ws->base + l.done, 0, (size_t)V * 4);
     if (e != cudaSuccess) { cudaFree(ws->base); delete ws; return cuda_fail(e, "workspace init"); }
     *out = ws;
     return ICR_OK;
@@ -174,16 +195,23 @@ static int compute_rewards_impl(const float* images, const void* labels, int lab
     ws->in = in;
     ws->t.V = t.V;
     const bool prof = ws->profile != 0;
+    const RewardArgs rw{image_sizes, rewards, S};
+    ws->prefix_valid = 0;
+    if (ws->dirty) {             // an earlier call died between prep and the tail kernel: its work lists were never reset
+        ICR_CUDA(cudaMemsetAsync(ws->t.sched, 0, (size_t)SCHED_N * 4, st), "reset work lists");
+        ws->dirty = 0;
+    }
+    ws->dirty = 1;
     if (prof) cudaEventRecord(ws->ev[0], st);
-    ICR_CUDA(launch_prep(labels, label_dtype, t, nullptr, st), "prep");
+    ICR_CUDA(launch_prep(labels, label_dtype, t, true, p.L_min, rw, st), "prep");
     if (prof) cudaEventRecord(ws->ev[1], st);
-    ICR_CUDA(launch_estimate(t, in, p, st), "estimate");
+    ICR_CUDA(launch_narrow(t, in, p, rw, st), "narrow");
     if (prof) cudaEventRecord(ws->ev[2], st);
-    bool fused = false;                                  // the big-segment kernel, when it runs, also does Rule W
-    ICR_CUDA(launch_big(t, in, p, image_sizes, rewards, &fused, st), "big_segment");
+    ICR_CUDA(launch_wide(t, in, p, rw, st), "wide");
     if (prof) cudaEventRecord(ws->ev[3], st);
-    if (!fused) ICR_CUDA(launch_reward(t, p, image_sizes, S, rewards, st), "reward");
+    ICR_CUDA(launch_big(t, in, p, rw, st), "big_segment");       // also resets the work lists and signals the peers
     if (prof) cudaEventRecord(ws->ev[4], st);
+    ws->dirty = 0;
     return ICR_OK;
 }
 
@@ -275,17 +303,23 @@ int icr_profile_read(icr_workspace* ws, float* ms4) {
     return ICR_OK;
 }
 
-int icr_check(icr_workspace* ws, icr_stream stream, int* first_bad) {
+int icr_check_detail(icr_workspace* ws, icr_stream stream, int* first_bad, int* status_bits, int* max_segments) {
     if (!ws) return fail(ICR_EINVAL, "workspace is null");
-    int32_t h[2] = {0, 0};
-    ICR_CUDA(cudaMemcpyAsync(h, ws->t.err, 8, cudaMemcpyDeviceToHost, (cudaStream_t)stream), "D2H error flag");
+    int32_t h[4] = {0, 0, 0, 0};
+    ICR_CUDA(cudaMemcpyAsync(h, ws->t.err, 16, cudaMemcpyDeviceToHost, (cudaStream_t)stream), "D2H error flag");
     ICR_CUDA(cudaStreamSynchronize((cudaStream_t)stream), "stream sync");
     if (first_bad) *first_bad = h[0] ? 0x7fffffff - h[1] : -1;
+    if (status_bits) *status_bits = h[0] ? h[2] : 0;
+    if (max_segments) *max_segments = h[0] ? h[3] : 0;
     if (!h[0]) return ICR_OK;
-    ICR_CUDA(cudaMemsetAsync(ws->t.err, 0, 8, (cudaStream_t)stream), "reset error flag");
-    return fail(ICR_EDATA, "label map " + std::to_string(0x7fffffff - h[1]) +
-                               ": label spread exceeds icr_label_capacity(H,W) or segment count exceeds Kmax; its reward is NaN");
+    ICR_CUDA(cudaMemsetAsync(ws->t.err, 0, 16, (cudaStream_t)stream), "reset error flag");
+    std::string why;
+    if (h[2] & ST_LABEL_RANGE) why += "label spread exceeds icr_label_capacity(H,W)";
+    if (h[2] & ST_K_OVERFLOW) why += std::string(why.empty() ? "" : "; ") + "segment count (up to " + std::to_string(h[3]) + ") exceeds Kmax";
+    return fail(ICR_EDATA, "label map " + std::to_string(0x7fffffff - h[1]) + ": " + why + "; the rewards of such maps are NaN");
 }
+
+int icr_check(icr_workspace* ws, icr_stream stream, int* first_bad) { return icr_check_detail(ws, stream, first_bad, nullptr, nullptr); }
 
 int icr_segment_stats(const void* labels, int label_dtype, int V, int H, int W, int32_t* K_out, int32_t* counts,
                       int32_t* bboxes, int32_t* compact_out, icr_workspace* ws, icr_stream stream) {
@@ -297,7 +331,9 @@ int icr_segment_stats(const void* labels, int label_dtype, int V, int H, int W, 
     t.V = V;
     ws->in = Inputs{nullptr, labels, label_dtype, 1};
     ws->t.V = V;
-    ICR_CUDA(launch_prep(labels, label_dtype, t, compact_out, st), "prep");
+    ws->prefix_valid = 0;
+    ICR_CUDA(launch_prep(labels, label_dtype, t, false, 4, RewardArgs{nullptr, nullptr, 1}, st), "prep");
+    if (compact_out) ICR_CUDA(launch_compact_ids(labels, label_dtype, t, compact_out, st), "compact ids");
     if (K_out) ICR_CUDA(cudaMemcpyAsync(K_out, t.K, (size_t)V * 4, cudaMemcpyDeviceToDevice, st), "copy K");
     if (counts) ICR_CUDA(cudaMemcpyAsync(counts, t.counts, (size_t)V * t.Kmax * 4, cudaMemcpyDeviceToDevice, st), "copy counts");
     if (bboxes) ICR_CUDA(cudaMemcpyAsync(bboxes, t.bboxes, (size_t)V * t.Kmax * 16, cudaMemcpyDeviceToDevice, st), "copy bboxes");
@@ -334,10 +370,12 @@ int icr_estimate_png_size_segment(const uint8_t* img, int full_W, int full_H, in
     ICR_CUDA(cudaGetDevice(&dev), "cudaGetDevice");
     if (dev < 0 || dev >= 16) return fail(ICR_EINVAL, "device index above 15");
     if (scratch_cap[dev] < h) {
-        if (scratch[dev]) { ICR_CUDA(cudaStreamSynchronize(st), "sync before scratch growth"); cudaFree(scratch[dev]); }
+        // stream-ordered: the old scratch is released behind the launches that use it, nothing waits on the host
+        if (scratch[dev]) ICR_CUDA(cudaFreeAsync(scratch[dev], st), "cudaFreeAsync(filter scratch)");
         scratch[dev] = nullptr; scratch_cap[dev] = 0;
-        ICR_CUDA(cudaMalloc((void**)&scratch[dev], (size_t)h), "cudaMalloc(filter scratch)");
-        scratch_cap[dev] = h;
+        int cap = h < 4096 ? 4096 : h;
+        ICR_CUDA(cudaMallocAsync((void**)&scratch[dev], (size_t)cap, st), "cudaMallocAsync(filter scratch)");
+        scratch_cap[dev] = cap;
     }
     ICR_CUDA(launch_single_segment(img, full_W, full_H, channels, labels, seg_id_k, x0, y0, w, h, widen(&prm), out_dev,
                                    dbg_row_costs, dbg_filter_id, dbg_hist, dbg_match, scratch[dev], st), "single segment");
@@ -363,8 +401,9 @@ int icr_debug_segment(icr_workspace* ws, int v, int k, const icr_params* params,
     if (v < 0 || v >= ws->t.V || k < 0 || k >= ws->Kmax) return fail(ICR_EINVAL, "segment index out of range");
     const EstParams p = widen(params);
     cudaStream_t st = (cudaStream_t)stream;
-    // both kernels test the Rule M size criterion on the device; exactly one of them acts
+    // the three kernels classify the segment on the device (segment_class); exactly one of them acts
     if (!ws->in.images) return fail(ICR_EINVAL, "no batch call has run on this workspace");
+    ICR_CUDA(launch_narrow_debug(ws->t, ws->in, p, v, k, row_costs, filter_id, hist, match, size_out, st), "narrow debug");
     ICR_CUDA(launch_estimate_debug(ws->t, ws->in, p, v, k, row_costs, filter_id, hist, match, size_out, st), "estimate debug");
     ICR_CUDA(launch_big_debug(ws->t, ws->in, p, v, k, row_costs, filter_id, hist, match, size_out, st), "big debug");
     return ICR_OK;
@@ -388,7 +427,8 @@ int icr_slices_prepare(const float* images, const void* labels, int label_dtype,
     t.V = B * S;
     ws->in = Inputs{images, labels, label_dtype, S};
     ws->t.V = t.V;
-    ICR_CUDA(launch_prep(labels, label_dtype, t, nullptr, (cudaStream_t)stream), "prep");
+    ws->prefix_valid = 0;
+    ICR_CUDA(launch_prep(labels, label_dtype, t, false, 4, RewardArgs{nullptr, nullptr, 1}, (cudaStream_t)stream), "prep");
     return ICR_OK;
 }
 
@@ -397,6 +437,10 @@ int icr_slices_plan(icr_workspace* ws, unsigned long long* offsets_dev, long lon
     if (!ws || !offsets_dev || !summary_dev) return fail(ICR_EINVAL, "null ptr");
     if (capacity < 1) return fail(ICR_EINVAL, "offsets capacity must be at least 1");
     if (!ws->in.labels) return fail(ICR_EINVAL, "no batch call has run on this workspace");
+    if (!ws->prefix_valid) {
+        ICR_CUDA(launch_seg_prefix(ws->t, (cudaStream_t)stream), "segment prefix");
+        ws->prefix_valid = 1;
+    }
     ICR_CUDA(launch_slice_plan(ws->t, offsets_dev, capacity, summary_dev, (cudaStream_t)stream), "slice plan");
     return ICR_OK;
 }

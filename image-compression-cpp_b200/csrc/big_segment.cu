@@ -369,70 +369,53 @@ __device__ void block_segment(const Src& src, int x0, int y0, int w, int h, int 
     __syncthreads();
 }
 
-__device__ __forceinline__ bool flagged(int4 bb, int L_min) { return for_big_kernel(bb.z - bb.x + 1, bb.w - bb.y + 1, L_min); }
-
-// Persistent CTAs walk the (label map, part) pairs.  Most maps hold no segment for this kernel: prep left the largest
-// bbox of every map, so those pairs cost two loads -- and, when Rule W is fused in (rewards != NULL), a warp computes
-// their reward up front.  Maps that do hold such segments split them over BIG_CTAS parts; the part that finishes last
-// computes the reward, every segment size of the map being final then.
+// Persistent CTAs pull the segments prep put on the back of list_other (Rule M can fire, or the bbox is wider or larger
+// than the warp paths take), one segment per CTA at a time.  This is always the last kernel of a batch call: whichever
+// CTA finishes last resets the work lists for the next call and, in a sharded run, tells the peers that this rank's
+// rewards have landed.
 template <typename LT>
-__global__ void __launch_bounds__(BIG_T, 4) big_kernel(Tables t, Inputs in, EstParams p, const double* __restrict__ image_sizes,
-                                                    double* __restrict__ rewards) {
-    __shared__ int s_last;
+__global__ void __launch_bounds__(BIG_T, 4) big_kernel(Tables t, Inputs in, EstParams p, RewardArgs rw) {
+    __shared__ int s_next, s_last;
     const int64_t HW = (int64_t)t.H * t.W;
     BigDebug none{};
-    // maps without such a segment: their sizes all come from the estimate kernel; a warp per map does Rule W
-    const bool do_rewards = rewards != nullptr || t.peer_rewards != nullptr;
-    if (do_rewards)
-        for (int v = blockIdx.x * (BIG_T / 32) + (threadIdx.x >> 5); v < t.V; v += gridDim.x * (BIG_T / 32)) {
-            const int2 mm = t.map_max[v];
-            if (t.status[v] != ST_OK || !map_may_need_big_kernel(mm.x, mm.y, p.L_min))
-                reward_of_map<false>(t, p, image_sizes, in.S, rewards, v, threadIdx.x & 31);
-        }
-    // all pairs of this CTA are looked at side by side first: usually none needs work and the CTA is done after one round trip
-    int mine = 0;
-    for (int pair = blockIdx.x + threadIdx.x * gridDim.x; pair < t.V * BIG_CTAS; pair += BIG_T * gridDim.x) {
-        const int2 mm = t.map_max[pair / BIG_CTAS];
-        mine |= t.status[pair / BIG_CTAS] == ST_OK && map_may_need_big_kernel(mm.x, mm.y, p.L_min);
-    }
-    const bool any_work = __syncthreads_or(mine) != 0;
-    for (int pair = blockIdx.x; any_work && pair < t.V * BIG_CTAS; pair += gridDim.x) {
-        const int v = pair / BIG_CTAS, part = (pair + v) % BIG_CTAS;      // rotated: part 0 of every map must not land on the same CTAs
-        const int2 mm = t.map_max[v];
-        if (t.status[v] != ST_OK || !map_may_need_big_kernel(mm.x, mm.y, p.L_min)) continue;
-        const int K = t.K[v];
-        const int4* bbs = t.bboxes + (int64_t)v * t.Kmax;
-        double* sizes = t.seg_sizes + (int64_t)v * t.Kmax;
-        uint8_t* filt = t.big_filter + ((int64_t)v * BIG_CTAS + part) * t.H;
-        for (int k0 = 0; k0 < K; k0 += BIG_T) {
-            const int k = k0 + threadIdx.x;
-            const int mine = (k < K && (k % BIG_CTAS) == part && flagged(__ldg(bbs + k), p.L_min)) ? 1 : 0;
-            if (!__syncthreads_or(mine)) continue;
-            const int kend = min(k0 + BIG_T, K);
-            for (int kk = k0 + ((part - k0) % BIG_CTAS + BIG_CTAS) % BIG_CTAS; kk < kend; kk += BIG_CTAS) {
-                const int4 bb = __ldg(bbs + kk);
-                if (!flagged(bb, p.L_min)) continue;
-                SrcPlanar<LT> src(in.images + (int64_t)(v / in.S) * 3 * HW, static_cast<const LT*>(in.labels) + (int64_t)v * HW, HW, t.W,
-                                  (LT)t.keys[(int64_t)v * t.Kmax + kk]);
-                block_segment(src, bb.x, bb.y, bb.z - bb.x + 1, bb.w - bb.y + 1, 4, p, filt, sizes + kk, none);
-            }
-        }
-        if (!do_rewards) continue;
+    const int total = t.sched[SC_N_BIG];
+    uint8_t* filt = t.big_filter + (int64_t)blockIdx.x * t.H;
+    for (;;) {
+        if (threadIdx.x == 0) s_next = total > 0 ? atomicAdd(&t.sched[SC_CUR_BIG], 1) : 0;
         __syncthreads();
-        if (threadIdx.x == 0) {
-            __threadfence();
-            s_last = atomicAdd(&t.big_done[v], 1) == BIG_CTAS - 1;
-            if (s_last) t.big_done[v] = 0;
+        const int i = s_next;
+        if (i >= total) break;
+        const uint2 e = t.list_other[t.list_cap - 1 - i];
+        const int v = (int)e.x, k = (int)e.y;
+        const int64_t row = (int64_t)v * t.Kmax + k;
+        const int4 bb = t.bboxes[row];
+        SrcPlanar<LT> src(in.images + (int64_t)(v / in.S) * 3 * HW, static_cast<const LT*>(in.labels) + (int64_t)v * HW, HW, t.W,
+                          (LT)t.keys[row]);
+        block_segment(src, bb.x, bb.y, bb.z - bb.x + 1, bb.w - bb.y + 1, 4, p, filt, t.seg_sizes + row, none);
+        if (threadIdx.x == 0) {                           // the thread that stored the size
+            s_last = segment_done(t, v, t.K[v]);
         }
         __syncthreads();
-        if (s_last && threadIdx.x < 32) {
+        if (s_last && threadIdx.x < 32) {                 // every size of this map is final: Rule W
             __threadfence();
-            reward_of_map<true>(t, p, image_sizes, in.S, rewards, v, threadIdx.x);
+            reward_of_map<true>(t, p, rw.image_sizes, rw.S, rw.rewards, v, threadIdx.x);
         }
-        __syncthreads();                                   // s_last is reused by the next pair
+        __syncthreads();                                  // s_next / s_last are reused
     }
-    signal_peers_when_grid_done(t, gridDim.x);
+    // ---- end of the batch call
+    __syncthreads();
+    if (threadIdx.x != 0) return;
+    if (t.peer_flags) __threadfence_system();             // this CTA's peer stores, if it wrote rewards
+    if (atomicAdd(&t.sched[SC_TAIL_DONE], 1) != (int)gridDim.x - 1) return;
+    for (int c = 0; c < SCHED_N; ++c) t.sched[c] = 0;
+    if (t.peer_flags) {
+        __threadfence_system();
+        for (int g = 0; g < t.peer_count; ++g)
+            asm volatile("st.release.sys.global.u64 [%0], %1;" :: "l"(t.peer_flags[g] + t.peer_rank), "l"(t.peer_step) : "memory");
+    }
 }
+
+__device__ __forceinline__ bool flagged(int4 bb, int L_min) { return segment_class(bb.z - bb.x + 1, bb.w - bb.y + 1, L_min) == CLS_BIG; }
 
 template <typename LT>
 __global__ void __launch_bounds__(BIG_T) big_debug_kernel(Tables t, Inputs in, EstParams p, int v, int k, BigDebug dbg) {
@@ -450,15 +433,11 @@ __global__ void __launch_bounds__(BIG_T) single_segment_kernel(SrcRaw src, int x
     block_segment(src, x0, y0, w, h, src.C, p, filt, out, dbg);
 }
 
-cudaError_t launch_big(const Tables& t, const Inputs& in, const EstParams& p, const double* image_sizes, double* rewards,
-                       bool* launched, cudaStream_t st) {
-    // no segment of an HxW map can need this kernel unless the whole map would
-    if (launched) *launched = false;
-    if (!for_big_kernel(t.W, t.H, p.L_min)) return cudaSuccess;
-    if (launched) *launched = true;
-    const int grid = min(t.V * BIG_CTAS, 148 * 4);
-    if (in.label_dtype == ICR_LABELS_I64) big_kernel<int64_t><<<grid, BIG_T, 0, st>>>(t, in, p, image_sizes, rewards);
-    else big_kernel<int32_t><<<grid, BIG_T, 0, st>>>(t, in, p, image_sizes, rewards);
+cudaError_t launch_big(const Tables& t, const Inputs& in, const EstParams& p, const RewardArgs& rw, cudaStream_t st) {
+    int grid = sm_count() * 4;
+    if (grid > BIG_GRID_MAX) grid = BIG_GRID_MAX;
+    if (in.label_dtype == ICR_LABELS_I64) big_kernel<int64_t><<<grid, BIG_T, 0, st>>>(t, in, p, rw);
+    else big_kernel<int32_t><<<grid, BIG_T, 0, st>>>(t, in, p, rw);
     count_launch();
     return cudaGetLastError();
 }

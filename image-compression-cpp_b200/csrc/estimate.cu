@@ -1,8 +1,10 @@
-// estimate: Rules C, P, F, R, H, Z for every (label map, segment) of the batch in ONE launch.
+// estimate (the "wide" kernel): Rules C, P, F, R, H, Z for the segments whose bbox is wider than the register path
+// takes (NARROW_MAX_W < w <= EST_MAX_W) and that need no match statistics, one warp per segment, one launch.
+// The bulk of a batch goes through narrow.cu; this is the shared-memory tile path that any width up to EST_MAX_W fits.
 // Replaces the reference's 13 stream operations per segment (src/png_size_estimator.cu:505-590),
 // its two nested host loops (src/compute_rewards.cu:125,159) and its RGBA staging kernel (:23-53).
 //
-// Persistent warps pull segments from the flat work list prep built, one per request with the next request in
+// Persistent warps pull segments from the work list prep built, one per request with the next request in
 // flight.  A warp owns one segment and walks its bbox in groups of R rows:
 //   stage    every lane takes pixels of the group as aligned quads in row-major order (coalesced, all lanes busy
 //            whatever the width).  The quads of group g+1 are requested with cp.async into the warp's raw window
@@ -22,6 +24,7 @@
 // need Rule M match statistics (chunk >= L_min) or are wider than EST_MAX_W go to the big-segment kernel.
 #include "icr_internal.h"
 #include "icr_pixel.cuh"
+#include "icr_reward.cuh"
 
 namespace icr {
 
@@ -47,11 +50,6 @@ struct __align__(16) WarpSmem {
     uint32_t pavg[PLANE_WORDS];       // Avg predictor of the group's pixels
     uint32_t ppae[PLANE_WORDS];       // Paeth predictor
     uint4 raw[RAW_BYTES / 16];        // the next row group's first quads as they lie in HBM (f32 planes, labels), filled by cp.async
-};
-
-struct DebugOut {
-    int v, k;
-    uint32_t* row_costs; uint8_t* filter_id; uint32_t* hist; unsigned long long* match; double* size;
 };
 
 // c*log2(c): table for the counts that occur in practice, one out-of-line copy of the slow path
@@ -82,26 +80,6 @@ __device__ __forceinline__ int choose_geometry(int w, int h, int lane) {
     // groups <= 2^20 (area cap of this path) and the bracket is below 400: cost * 8 fits 32 bits
     const uint32_t key = __reduce_min_sync(0xffffffffu, ok ? cost * 8u + (uint32_t)l : 0xffffffffu);
     return key == 0xffffffffu ? 5 : (int)(key & 7u);
-}
-
-// The map v with seg_prefix[v] <= flat < seg_prefix[v+1], searched by the whole warp: 32 probes per round, so two
-// dependent loads for up to 1024 maps instead of a lane's ten-step binary search.  seg_prefix[v] itself comes out of
-// the probes (the last probe that was <= flat, handed over by a shuffle), which saves the dependent load after the search.
-__device__ __forceinline__ int locate_map(const int32_t* __restrict__ sp, int V, int flat, int lane, int& first) {
-    int lo = 0, n = V;                                  // answer in [lo, lo+n); sp[lo] <= flat
-    first = 0;                                          // sp[lo]; seg_prefix[0] = 0
-    while (n > 1) {
-        const int step = (n + 31) >> 5;
-        const int idx = lo + (lane + 1) * step;
-        const int val = idx < lo + n ? __ldg(sp + idx) : 0x7fffffff;
-        const bool le = val <= flat;                                   // monotone in lane
-        const int c = __popc(__ballot_sync(0xffffffffu, le));
-        const int hit = __shfl_sync(0xffffffffu, val, (c + 31) & 31);  // lane c-1 holds sp[lo + c*step]
-        if (c) first = hit;
-        lo += c * step;
-        n = min(step, n - c * step);
-    }
-    return lo;
 }
 
 // One request to the work list.  Plain PTX: through atomicAdd the compiler aggregates the (single-lane) atomic over the
@@ -445,7 +423,7 @@ __device__ void warp_segment(const float* __restrict__ img, const LT* __restrict
 }
 
 template <typename LT, bool VEC>
-__global__ void __launch_bounds__(EST_WARPS * 32, 4) estimate_kernel(Tables t, Inputs in, EstParams p) {
+__global__ void __launch_bounds__(EST_WARPS * 32, 4) estimate_kernel(Tables t, Inputs in, EstParams p, RewardArgs rw) {
     extern __shared__ __align__(16) unsigned char est_smem[];
     WarpSmem* wsm = reinterpret_cast<WarpSmem*>(est_smem);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -453,28 +431,31 @@ __global__ void __launch_bounds__(EST_WARPS * 32, 4) estimate_kernel(Tables t, I
     for (int i = lane; i < 1024; i += 32) sm.hist[i] = 0;
     __syncwarp();
     const int64_t HW = (int64_t)t.H * t.W;
-    const int total = t.seg_prefix[t.V];
+    const int total = t.sched[SC_N_WIDE];
     const LT* labels = static_cast<const LT*>(in.labels);
     DebugOut none{};
-    // One segment per request: a warp's share of the SM makes a segment take ~15 us, so handing out several at a time left
-    // warps idle for tens of microseconds at the end of the launch.  The request for the next segment is issued before
-    // the current one is worked on, so its latency is hidden.
+    // One segment per request; the request for the next segment is issued before the current one is worked on.
     int flat = 0;
-    if (lane == 0) flat = next_segment(&t.sched[1]);
+    if (lane == 0) flat = next_segment(&t.sched[SC_CUR_WIDE]);
     flat = __shfl_sync(0xffffffffu, flat, 0);
     while (flat < total) {
         int fut = 0;
-        if (lane == 0) fut = next_segment(&t.sched[1]);
-        int first;
-        const int v = locate_map(t.seg_prefix, t.V, flat, lane, first);
-        const int k = flat - first;
+        if (lane == 0) fut = next_segment(&t.sched[SC_CUR_WIDE]);
+        const uint2 e = __ldg(t.list_other + flat);
+        const int v = (int)e.x, k = (int)e.y;
         const int64_t row = (int64_t)v * t.Kmax + k;
         const int4 bb = __ldg(t.bboxes + row);
         const LT key = (LT)__ldg(t.keys + row);
         const int count = __ldg(t.counts + row);
-        if (!for_big_kernel(bb.z - bb.x + 1, bb.w - bb.y + 1, p.L_min))
-            warp_segment<LT, false, VEC>(in.images + (int64_t)(v / in.S) * 3 * HW, labels + (int64_t)v * HW, HW, t.W, key, count, bb, sm, p,
-                                         t.clog2, t.seg_sizes + row, none);
+        const int K = __ldg(t.K + v);
+        warp_segment<LT, false, VEC>(in.images + (int64_t)(v / in.S) * 3 * HW, labels + (int64_t)v * HW, HW, t.W, key, count, bb, sm, p,
+                                     t.clog2, t.seg_sizes + row, none);
+        int last = 0;
+        if (lane == 0) last = segment_done(t, v, K);       // lane 0 stored the size
+        if (__shfl_sync(0xffffffffu, last, 0)) {         // every size of this map is final: Rule W
+            __threadfence();
+            reward_of_map<true>(t, p, rw.image_sizes, rw.S, rw.rewards, v, lane);
+        }
         flat = __shfl_sync(0xffffffffu, fut, 0);
     }
 }
@@ -487,7 +468,7 @@ __global__ void __launch_bounds__(32) estimate_debug_kernel(Tables t, Inputs in,
     __syncwarp();
     const int64_t HW = (int64_t)t.H * t.W;
     const int4 bb = t.bboxes[(int64_t)dbg.v * t.Kmax + dbg.k];
-    if (for_big_kernel(bb.z - bb.x + 1, bb.w - bb.y + 1, p.L_min)) return;     // the big-segment debug kernel acts
+    if (segment_class(bb.z - bb.x + 1, bb.w - bb.y + 1, p.L_min) != CLS_WIDE) return;     // another debug kernel acts
     const LT key = (LT)t.keys[(int64_t)dbg.v * t.Kmax + dbg.k];
     double scratch;
     warp_segment<LT, true, VEC>(in.images + (int64_t)(dbg.v / in.S) * 3 * HW, static_cast<const LT*>(in.labels) + (int64_t)dbg.v * HW,
@@ -501,28 +482,30 @@ static bool vec_ok(const Tables& t, const Inputs& in) {
 }
 
 template <typename LT, bool VEC>
-static cudaError_t launch_est_t(const Tables& t, const Inputs& in, const EstParams& p, cudaStream_t st) {
-    static int grid = 0;
+static cudaError_t launch_est_t(const Tables& t, const Inputs& in, const EstParams& p, const RewardArgs& rw, cudaStream_t st) {
+    static int per_sm[16] = {0};          // resident CTAs per SM, per device (function attributes are per device too)
     const size_t smem = sizeof(WarpSmem) * EST_WARPS;
     auto kern = estimate_kernel<LT, VEC>;
-    if (!grid) {
-        int dev = 0, sms = 148, per = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    int per = (dev >= 0 && dev < 16) ? per_sm[dev] : 0;
+    if (!per) {
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, kern, EST_WARPS * 32, smem);
         if (e != cudaSuccess) return e;
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, kern, EST_WARPS * 32, smem);
-        grid = sms * (per < 1 ? 1 : per);     // persistent: every CTA resident, warps pull work until the list is empty
+        if (per < 1) per = 1;
+        if (dev >= 0 && dev < 16) per_sm[dev] = per;
     }
-    kern<<<grid, EST_WARPS * 32, smem, st>>>(t, in, p);
+    kern<<<sm_count() * per, EST_WARPS * 32, smem, st>>>(t, in, p, rw);     // persistent: warps pull work until the list is empty
     count_launch();
     return cudaGetLastError();
 }
 
-cudaError_t launch_estimate(const Tables& t, const Inputs& in, const EstParams& p, cudaStream_t st) {
+cudaError_t launch_wide(const Tables& t, const Inputs& in, const EstParams& p, const RewardArgs& rw, cudaStream_t st) {
     const bool vec = vec_ok(t, in);
-    if (in.label_dtype == ICR_LABELS_I64) return vec ? launch_est_t<int64_t, true>(t, in, p, st) : launch_est_t<int64_t, false>(t, in, p, st);
-    return vec ? launch_est_t<int32_t, true>(t, in, p, st) : launch_est_t<int32_t, false>(t, in, p, st);
+    if (in.label_dtype == ICR_LABELS_I64) return vec ? launch_est_t<int64_t, true>(t, in, p, rw, st) : launch_est_t<int64_t, false>(t, in, p, rw, st);
+    return vec ? launch_est_t<int32_t, true>(t, in, p, rw, st) : launch_est_t<int32_t, false>(t, in, p, rw, st);
 }
 
 template <typename LT, bool VEC>

@@ -20,13 +20,22 @@ struct Tables {            // device pointers into the workspace, V label maps
     long long* keys;       // [V,Kmax] original label value of compact id k (ascending: Rule L)
     double* seg_sizes;     // [V,Kmax]
     int32_t* err;          // [2] {any-error flag, 0x7fffffff - first bad map}
-    int32_t* seg_prefix;   // [V+1] exclusive scan of the segment counts of the maps with status OK
-    int32_t* sched;        // [4] {prep CTAs done, estimate work cursor, -, -}
-    uint8_t* big_filter;   // [V*BIG_CTAS, H] filter ids of the segment a big-kernel CTA is working on
-    uint2* runs;           // [V, run_cap] label runs of a map found by prep's first sweep {slot | (len-1)<<20, y<<16 | x}
-    int run_cap;           // 0 = no run list (very wide maps)
-    int2* map_max;         // [V] {largest bbox area, widest bbox} of a map (INT_MAX when not known): lets the big-segment kernel skip maps
-    int32_t* big_done;     // [V] big-segment CTAs of a map that have finished (self-resetting)
+    int32_t* seg_prefix;   // [V+1] exclusive scan of the segment counts of the maps with status OK (built on demand for the slices)
+    int32_t* sched;        // [SCHED_N] work-list lengths, cursors and kernel-internal counters, see the SC_* indices
+    uint8_t* big_filter;   // [BIG_GRID_MAX, H] filter ids of the segment a big-kernel CTA is working on
+    uint32_t* heads;       // [V, head_cap] pixel index of every label-run head of a map, ascending (prep)
+    uint32_t* hslot;       // [V, head_cap] bitmap slot of the head's label
+    int head_cap;          // run heads a map's list holds (an average run of 8 pixels fits); beyond it prep walks the change bitmap
+    uint8_t* chg_global;   // [V, chg_stride] change bitmap of a map when it does not fit shared memory, else NULL
+    int64_t chg_stride;
+    // Work lists prep leaves for the estimator kernels: entries {label map v, compact id k}.  list_narrow holds the
+    // segments of the register path (bbox no wider than NARROW_MAX_W): the larger ones from the front, the smaller ones
+    // from the back, so that the kernel starts with the long ones.  list_other: wide segments (shared-memory path) from
+    // the front, Rule M / very large segments (CTA per segment) from the back.
+    uint2* list_narrow;    // [list_cap]
+    uint2* list_other;     // [list_cap]
+    int64_t list_cap;
+    int32_t* done;         // [V] segments of a map whose size has been written; the writer of the last one computes Rule W
     unsigned long long* slice_map_off;   // [V] byte offset of a map's first slice in the packed slice buffer (slices.cu)
     const double* clog2;   // [CLOG2_N] c*log2(c)
     // multi-GPU gather fused into the reward writer (icr_compute_rewards_gather): the reward of map v also goes to
@@ -49,8 +58,14 @@ struct Inputs {            // the caller's device buffers of the current call
     int S;                 // label maps per image
 };
 
-constexpr int BIG_CTAS = 2;       // big-segment CTAs per label map
 constexpr int CLOG2_N = 4096;
+constexpr int NARROW_MAX_W = 64;  // widest bbox of the register path (two 32-lane chunks per row)
+constexpr int LPT_AREA = 768;     // narrow segments with a larger bbox are handed out first
+constexpr int BIG_GRID_MAX = 148 * 8;
+
+// t.sched[]: list lengths are written by prep, cursors by the consuming kernels; the tail kernel's last CTA zeroes them
+enum : int { SC_N_LARGE = 0, SC_N_SMALL, SC_N_WIDE, SC_N_BIG, SC_CUR_NARROW, SC_CUR_WIDE, SC_CUR_BIG, SC_TAIL_DONE, SC_PEER_DONE,
+             SC_PREP_DONE, SCHED_N = 16 };
 constexpr int EST_MAX_W = 224;    // widest bbox of the warp path: a one-row group (two row slots) must fit the warp's tile
 constexpr int EST_MAX_AREA = 1 << 20;
 
@@ -67,6 +82,11 @@ __host__ __device__ inline bool map_may_need_big_kernel(int area, int maxw, int 
     return (4ll * area + 65535) / 65536 >= (long long)L_min || maxw > EST_MAX_W || (long long)area > EST_MAX_AREA;
 }
 
+struct DebugOut {          // per-segment tables the debug entry fills (device pointers, may be NULL)
+    int v, k;
+    uint32_t* row_costs; uint8_t* filter_id; uint32_t* hist; unsigned long long* match; double* size;
+};
+
 struct EstParams {         // icr_params widened the way the reference does (:588)
     int32_t min_pixels, L_min, adaptive;
     double beta, token, gamma, overhead, lambda;
@@ -82,22 +102,40 @@ inline int64_t label_capacity(int H, int W) {
     return cap;
 }
 
-// run-list capacity per map: an average run of 8 pixels or more fits; beyond it prep falls back to a second pixel sweep
-inline int run_capacity(int H, int W) {
-    if (W > 4096 || H > 65535) return 0;          // record packing: 12 bits of length, 16 bits of x and y
+// run-head list capacity per map: an average run of 8 pixels or more fits; beyond it prep walks the change bitmap instead
+inline int head_capacity(int H, int W) {
     int64_t c = (int64_t)H * W / 8;
     return (int)(c < 1024 ? 1024 : c);
 }
 
+// bytes of a map's change bitmap (one bit per pixel, padded to whole 32-bit words)
+inline int64_t chg_bytes(int H, int W) { return (((int64_t)H * W + 31) / 32) * 4; }
+
+// shared memory prep needs next to its static arrays: presence bitmap + max(change bitmap, popcount prefix) + stats table.
+// The change bitmap moves to global memory when that exceeds what a CTA may have.
+constexpr int64_t PREP_SMEM_MAX = 200 * 1024;
+inline bool chg_in_smem(int H, int W) {
+    const int64_t cap_b = label_capacity(H, W) / 8, cb = chg_bytes(H, W);
+    return cap_b + (cb > cap_b ? cb : cap_b) + (int64_t)KS_SMEM * 20 <= PREP_SMEM_MAX;
+}
+
 // launchers (each returns the cudaError_t of its launches)
-cudaError_t launch_prep(const void* labels, int label_dtype, const Tables& t, int32_t* compact_out, cudaStream_t st);
-cudaError_t launch_estimate(const Tables& t, const Inputs& in, const EstParams& p, cudaStream_t st);
-// image_sizes/rewards non-null: the last big-segment CTA of each map also computes the map's reward (Rule W), so the
-// reward kernel is not launched; *launched tells whether the kernel ran at all
-cudaError_t launch_big(const Tables& t, const Inputs& in, const EstParams& p, const double* image_sizes, double* rewards,
-                       bool* launched, cudaStream_t st);
-cudaError_t launch_reward(const Tables& t, const EstParams& p, const double* image_sizes, int S,
-                          double* rewards, cudaStream_t st);
+// what the kernels that write segment sizes need for Rule W: whoever writes the last size of a map computes its reward
+struct RewardArgs { const double* image_sizes; double* rewards; int S; };
+
+// lists = true: build the estimator's work lists (batch path); false: tables only (icr_segment_stats, icr_slices_prepare).
+// Maps that cannot be processed get a NaN reward from prep itself when rw.rewards (or the peer vectors) are set.
+cudaError_t launch_prep(const void* labels, int label_dtype, const Tables& t, bool lists, int L_min, const RewardArgs& rw,
+                        cudaStream_t st);
+cudaError_t launch_compact_ids(const void* labels, int label_dtype, const Tables& t, int32_t* compact_out, cudaStream_t st);
+cudaError_t launch_seg_prefix(const Tables& t, cudaStream_t st);
+cudaError_t launch_narrow(const Tables& t, const Inputs& in, const EstParams& p, const RewardArgs& rw, cudaStream_t st);
+cudaError_t launch_wide(const Tables& t, const Inputs& in, const EstParams& p, const RewardArgs& rw, cudaStream_t st);
+// always the last kernel of a batch call: Rule M segments, then its last CTA resets the work lists and signals the peers
+cudaError_t launch_big(const Tables& t, const Inputs& in, const EstParams& p, const RewardArgs& rw, cudaStream_t st);
+cudaError_t launch_narrow_debug(const Tables& t, const Inputs& in, const EstParams& p, int v, int k, uint32_t* row_costs,
+                                uint8_t* filter_id, uint32_t* hist, unsigned long long* match,
+                                double* size_out, cudaStream_t st);
 cudaError_t launch_estimate_debug(const Tables& t, const Inputs& in, const EstParams& p, int v, int k, uint32_t* row_costs,
                                   uint8_t* filter_id, uint32_t* hist, unsigned long long* match,
                                   double* size_out, cudaStream_t st);
@@ -125,5 +163,13 @@ cudaError_t launch_sum_count(const double* rewards, int n, double* sum_count, cu
 cudaError_t run_selftest(int* mismatches);
 
 void count_launch(int n = 1);
+int sm_count();            // multiprocessors of the current device (cached per device)
+
+// which kernel takes a segment with a w x h bbox
+enum : int { CLS_NARROW = 0, CLS_WIDE = 1, CLS_BIG = 2 };
+__host__ __device__ inline int segment_class(int w, int h, int L_min) {
+    if (for_big_kernel(w, h, L_min)) return CLS_BIG;
+    return w > NARROW_MAX_W ? CLS_WIDE : CLS_NARROW;
+}
 
 }  // namespace icr

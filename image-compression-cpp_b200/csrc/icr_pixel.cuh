@@ -32,7 +32,7 @@ __device__ __forceinline__ uint32_t rgba_of(float r, float g, float b) {
 __device__ __forceinline__ uint32_t absdiff4(uint32_t a, uint32_t b) { return __vabsdiffu4(a, b); }
 
 // (a+b)>>1 per byte, no carry between bytes (Avg predictor, :140-145)
-__device__ __forceinline__ uint32_t avg4(uint32_t a, uint32_t b) { return __vhaddu4(a, b); }
+__device__ __forceinline__ uint32_t avg4(uint32_t a, uint32_t b) { return (a & b) + (((a ^ b) & 0xfefefefeu) >> 1); }
 
 // bytes (lo, lo+1) of x as half2 {1024+b_lo, 1024+b_hi}: 0x64xx is 1024+xx in fp16, exact.
 __device__ __forceinline__ uint32_t unpack_lo(uint32_t x) { return __byte_perm(x, 0x64646464u, 0x5140); }
@@ -54,6 +54,33 @@ __device__ __forceinline__ uint32_t paeth_h2(uint32_t A, uint32_t B, uint32_t C)
     __half2 mb = __hle2(pb, pc);
     __half2 bc = __hfma2(mb, da, as_h2(C));
     __half2 r = __hfma2(ma, __hsub2(as_h2(A), bc), bc);
+    return *reinterpret_cast<uint32_t*>(&r);
+}
+
+// The same select with every step on the FMA pipe (no HSET2 / HMNMX2, which share the ALU pipe with the byte
+// arithmetic): for integer-valued t, sat(t) is the indicator [t >= 1] and relu(t) = max(t, 0), so
+//   nb = [pb > pc] = sat(pb - pc),   na = [pa > min(pb, pc)] = sat((pa - pb) + relu(pb - pc)),
+//   result = A + na * ((nb ? C : B) - A).  Ten instructions per two channels, all HADD2 / HFMA2.
+__device__ __forceinline__ uint32_t paeth_h2_fma(uint32_t A, uint32_t B, uint32_t C) {
+    const __half2 one = __float2half2_rn(1.0f);
+    __half2 da = __hsub2(as_h2(B), as_h2(C));      // p - a
+    __half2 db = __hsub2(as_h2(A), as_h2(C));      // p - b
+    __half2 dc = __hadd2(da, db);                  // p - c
+    __half2 pa = __habs2(da), pb = __habs2(db), pc = __habs2(dc);
+    __half2 nb = __hfma2_sat(pb, one, __hneg2(pc));
+    __half2 t1 = __hfma2_relu(pb, one, __hneg2(pc));
+    __half2 t2 = __hsub2(pa, pb);
+    __half2 na = __hadd2_sat(t2, t1);
+    __half2 bc = __hfma2(nb, __hneg2(da), as_h2(B));
+    __half2 e = __hsub2(bc, as_h2(A));
+    __half2 r = __hfma2(na, e, as_h2(A));
+    return *reinterpret_cast<uint32_t*>(&r);
+}
+
+// residual bytes of two channels held as biased half2 {1024+cur} and {1024+pred}: (cur - pred) + 1280 lies in
+// [1025, 1535], where fp16 has unit spacing, so the low byte of each half of the result is (cur - pred) mod 256
+__device__ __forceinline__ uint32_t residual_h2(uint32_t cur, uint32_t pred) {
+    __half2 r = __hadd2(__hsub2(as_h2(cur), as_h2(pred)), __float2half2_rn(1280.0f));
     return *reinterpret_cast<uint32_t*>(&r);
 }
 

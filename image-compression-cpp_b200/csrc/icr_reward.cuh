@@ -1,6 +1,6 @@
-// Rule W (src/compute_rewards.cu:183-192) for one label map by one warp, fixed summation order.  Shared by the reward
-// kernel and by the big-segment kernel's last CTA of a map.  VOLATILE: segment sizes may have been written by other CTAs
-// of the running kernel, so they are read past L1.
+// Rule W (src/compute_rewards.cu:183-192) for one label map by one warp, fixed summation order.  Called by whichever
+// warp stored the last segment size of the map (narrow.cu, estimate.cu, big_segment.cu count finished segments in
+// Tables::done).  VOLATILE: segment sizes may have been written by other CTAs of the running kernel, so they are read past L1.
 #pragma once
 #include "icr_internal.h"
 
@@ -9,23 +9,19 @@ namespace icr {
 // one reward to the caller's buffer and, when the call gathers, to the same slot of every rank's gathered vector
 __device__ __forceinline__ void store_reward(const Tables& t, double* __restrict__ rewards, int v, double r) {
     if (rewards) rewards[v] = r;
-    if (t.peer_rewards)
+    if (t.peer_rewards) {
         for (int g = 0; g < t.peer_count; ++g) t.peer_rewards[g][t.peer_offset + v] = r;
+        __threadfence_system();         // ordered before the flag the last CTA of the batch's last kernel raises (big_segment.cu)
+    }
 }
 
-// Called by every CTA of a reward-writing kernel as its last action.  Each CTA makes its peer stores visible system-wide
-// and counts itself in; the CTA that finds all others done tells every rank that this rank's rewards of step peer_step
-// have landed.  Release/acquire at system scope pairs with the wait in the EMA kernel.
-__device__ __forceinline__ void signal_peers_when_grid_done(const Tables& t, int ctas) {
-    if (!t.peer_flags) return;
-    __syncthreads();
-    if (threadIdx.x != 0) return;
-    __threadfence_system();
-    if (atomicAdd(&t.sched[2], 1) != ctas - 1) return;
-    t.sched[2] = 0;
-    __threadfence_system();
-    for (int g = 0; g < t.peer_count; ++g)
-        asm volatile("st.release.sys.global.u64 [%0], %1;" :: "l"(t.peer_flags[g] + t.peer_rank), "l"(t.peer_step) : "memory");
+// Called by the thread that has just stored the size of one segment of label map v: counts it in, ordered after the
+// store (release at device scope: no L1 invalidation, unlike a full fence), and tells whether it was the map's last.
+// The caller of the last one fences (acquire side) before it reads the other sizes past L1 in reward_of_map.
+__device__ __forceinline__ int segment_done(const Tables& t, int v, int K) {
+    int old;
+    asm volatile("atom.add.release.gpu.global.s32 %0, [%1], 1;" : "=r"(old) : "l"(t.done + v) : "memory");
+    return old == K - 1;
 }
 
 template <bool VOLATILE>

@@ -1,24 +1,10 @@
-// Small kernels around the estimator: reward epilogue (Rule W), slice materialisation (Rule P),
+// Small kernels around the estimator: slice materialisation of one segment (Rule P),
 // the compact-label stats drop-in (Rule S), EMA baseline + advantage (Rule E) and the self-test.
 #include "icr_internal.h"
 #include "icr_pixel.cuh"
 #include "icr_reward.cuh"
 
 namespace icr {
-
-// ---- Rule W (src/compute_rewards.cu:183-192): one warp per label map, fixed summation order
-__global__ void __launch_bounds__(128) reward_kernel(Tables t, EstParams p, const double* __restrict__ image_sizes,
-                                                      int S, double* __restrict__ rewards) {
-    const int v = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
-    if (v < t.V) reward_of_map<false>(t, p, image_sizes, S, rewards, v, lane);
-    signal_peers_when_grid_done(t, gridDim.x);
-}
-
-cudaError_t launch_reward(const Tables& t, const EstParams& p, const double* image_sizes, int S, double* rewards, cudaStream_t st) {
-    reward_kernel<<<(t.V + 3) / 4, 128, 0, st>>>(t, p, image_sizes, S, rewards);
-    count_launch();
-    return cudaGetLastError();
-}
 
 // ---- Rule P (src/image_slicer.cpp:59-66): masked bbox crop of one segment, u8 [h,w,4]
 template <typename LT>
@@ -44,8 +30,8 @@ __global__ void slice_kernel(Tables t, Inputs in, int v, int k, uint32_t* out, s
 }
 
 cudaError_t launch_slice(const Tables& t, const Inputs& in, int v, int k, uint8_t* out, size_t cap, cudaStream_t st) {
-    if (in.label_dtype == ICR_LABELS_I64) slice_kernel<int64_t><<<148, 256, 0, st>>>(t, in, v, k, reinterpret_cast<uint32_t*>(out), cap / 4);
-    else slice_kernel<int32_t><<<148, 256, 0, st>>>(t, in, v, k, reinterpret_cast<uint32_t*>(out), cap / 4);
+    if (in.label_dtype == ICR_LABELS_I64) slice_kernel<int64_t><<<sm_count(), 256, 0, st>>>(t, in, v, k, reinterpret_cast<uint32_t*>(out), cap / 4);
+    else slice_kernel<int32_t><<<sm_count(), 256, 0, st>>>(t, in, v, k, reinterpret_cast<uint32_t*>(out), cap / 4);
     count_launch();
     return cudaGetLastError();
 }
@@ -87,7 +73,7 @@ cudaError_t launch_compact_stats(const int64_t* labels, int H, int W, int K, int
     if (K > 0) { compact_init_kernel<<<(K + 255) / 256, 256, 0, st>>>(counts, bboxes, K, W, H); count_launch(); }
     const int64_t HW = (int64_t)H * W;
     int blocks = (int)((HW + 255) / 256);
-    if (blocks > 148 * 16) blocks = 148 * 16;
+    if (blocks > sm_count() * 16) blocks = sm_count() * 16;
     if (blocks > 0) { compact_stats_kernel<<<blocks, 256, 0, st>>>(labels, H, W, K, counts, bboxes); count_launch(); }
     return cudaGetLastError();
 }
@@ -113,7 +99,9 @@ __global__ void __launch_bounds__(1024) sum_count_kernel(const double* __restric
 
 // flags != NULL: r is this rank's gathered vector, filled by all ranks' reward kernels through peer memory; wait until
 // every rank has signalled step `step` (bounded: a rank that never arrives poisons the baseline instead of hanging the GPU)
-__global__ void __launch_bounds__(1024) ema_kernel(const double* __restrict__ r, int n, const double* sum_count,
+// r is read past L1 and without the read-only path: on the gathered path it is being written by peer GPUs while this kernel
+// already runs, and only the acquire on the flags orders those writes before the reads below
+__global__ void __launch_bounds__(1024) ema_kernel(const double* r, int n, const double* sum_count,
                                                     double momentum, double* state, double* adv,
                                                     const unsigned long long* flags, int ranks, unsigned long long step) {
     __shared__ double sh[32];
@@ -133,7 +121,7 @@ __global__ void __launch_bounds__(1024) ema_kernel(const double* __restrict__ r,
         if (s_timeout) { if (threadIdx.x == 0) { state[0] = __longlong_as_double(0x7ff8000000000000ll); state[1] = 1.0; } return; }
     }
     double s = 0.0;
-    for (int i = threadIdx.x; i < n; i += blockDim.x) s += r[i];
+    for (int i = threadIdx.x; i < n; i += blockDim.x) s += __ldcg(r + i);
     s = block_sum(s, sh);
     const double local_mean = n > 0 ? s / (double)n : 0.0;
     const double mean = sum_count ? sum_count[0] / sum_count[1] : local_mean;
@@ -146,12 +134,12 @@ __global__ void __launch_bounds__(1024) ema_kernel(const double* __restrict__ r,
     if (!adv) return;
     // adv = (r - value); standardise: the baseline cancels in (adv - mean(adv)), std is the population std
     double q = 0.0;
-    for (int i = threadIdx.x; i < n; i += blockDim.x) { double d = r[i] - local_mean; q += d * d; }
+    for (int i = threadIdx.x; i < n; i += blockDim.x) { double d = __ldcg(r + i) - local_mean; q += d * d; }
     q = block_sum(q, sh);
     const double sd = fmax(sqrt(q / (double)n), 1e-6);
     const double value = s_value;
     const double adv_mean = local_mean - value;
-    for (int i = threadIdx.x; i < n; i += blockDim.x) adv[i] = ((r[i] - value) - adv_mean) / sd;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) adv[i] = ((__ldcg(r + i) - value) - adv_mean) / sd;
 }
 
 cudaError_t launch_sum_count(const double* rewards, int n, double* sum_count, cudaStream_t st) {

@@ -172,7 +172,7 @@ cudaError_t launch_slice_plan(const Tables& t, unsigned long long* offsets, long
 cudaError_t launch_slice_emit(const Tables& t, const Inputs& in, const unsigned long long* offsets, uint8_t* out, size_t cap,
                               int swap, cudaStream_t st) {
     if (t.V <= 0) return cudaSuccess;
-    const long long resident = 148 * 32;                            // CTAs the machine holds at once (32 registers, 64 threads)
+    const long long resident = (long long)sm_count() * 32;           // CTAs the machine holds at once (32 registers, 64 threads)
     const long long map_bytes = (long long)t.H * t.W * (12 + (in.label_dtype == ICR_LABELS_I64 ? 8 : 4));
     const long long in_flight = std::max(1ll, (48ll << 20) / std::max(1ll, map_bytes));      // maps that share the L2 comfortably
     long long P = std::min(1024ll, (resident + in_flight - 1) / in_flight);                  // CTAs per map
@@ -256,10 +256,10 @@ cudaError_t launch_reassemble(const Tables& t, int v0, int nmaps, const unsigned
     cudaError_t e = cudaMemsetAsync(canvases, 0, map_bytes * (size_t)nmaps, st);   // cv::Scalar(0,0,0,0), :50
     if (e != cudaSuccess) return e;
     // CTAs per map: enough that the maps in flight (canvas + slices, ~2.5x the canvas) share the L2, see launch_slice_emit
-    const long long resident = 148 * 32;
+    const long long resident = (long long)sm_count() * 32;
     const long long in_flight = std::max(1ll, (48ll << 20) / std::max<long long>(1, (long long)map_bytes * 5 / 2));
     long long P = std::min(1024ll, (resident + in_flight - 1) / in_flight);
-    if (nmaps == 1) P = 148 * 4;
+    if (nmaps == 1) P = sm_count() * 4;
     while (P > 1 && P * nmaps > (1ll << 30)) P >>= 1;
     reassemble_kernel<<<(unsigned)(P * nmaps), EMIT_T, 0, st>>>(t, v0, (int)P, offsets, reinterpret_cast<const uint32_t*>(slices),
                                                                 reinterpret_cast<uint32_t*>(canvases));
@@ -270,7 +270,7 @@ cudaError_t launch_reassemble(const Tables& t, int v0, int nmaps, const unsigned
 cudaError_t launch_paste(uint8_t* canvas, int W, int H, const uint8_t* slice, int x, int y, int w, int h, cudaStream_t st) {
     const int cw = min(w, W - x), ch = min(h, H - y);                              // :58-59
     if (cw <= 0 || ch <= 0) return cudaSuccess;                                    // "lies outside canvas, skipping", :61-64
-    const int grid = min((ch + 7) / 8, 148 * 4);
+    const int grid = min((ch + 7) / 8, sm_count() * 4);
     paste_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<uint32_t*>(canvas), W, H, reinterpret_cast<const uint32_t*>(slice), x, y, w, cw, ch);
     count_launch();
     return cudaGetLastError();

@@ -101,6 +101,10 @@ int icr_compute_rewards_host(const float* images_h, const void* labels_h, int la
  * if a label map's value spread exceeded the capacity or its K exceeded Kmax; rewards of such
  * maps are NaN.  The reference has the same one-sync-per-call behaviour, only 2 per image. */
 int icr_check(icr_workspace* ws, icr_stream stream, int* first_bad);
+/* Same, with the reason: *status_bits = OR over the failed maps of 1 (label spread beyond the capacity: rank the labels first,
+ * as at::_unique at src/compute_rewards.cu:132 would) and 2 (more segments than Kmax: *max_segments tells how many table
+ * rows the largest such map needs).  Outputs may be NULL. */
+int icr_check_detail(icr_workspace* ws, icr_stream stream, int* first_bad, int* status_bits, int* max_segments);
 int64_t icr_label_capacity(int H, int W);
 
 /* ---- segment_stats batched, with Rule L folded in (src/compute_rewards.cu:131-141 +
@@ -201,8 +205,9 @@ int icr_ema_update_gathered(const double* gathered, int n, const unsigned long l
 int icr_selftest(int* mismatches);
 
 /* Measurement hook: with profiling on, icr_compute_rewards records CUDA events on `stream` between its
- * kernels; icr_profile_read waits for the last call and returns the device time in ms of
- * {prep, estimate, big_segment, reward}. */
+ * kernels; icr_profile_read waits for the last call and returns the device time in ms of its four launches
+ * {prep (Rules L, S + work lists), narrow (register path: bboxes up to 64 wide), wide (shared-memory path),
+ *  big_segment (Rule M segments + end-of-call bookkeeping)}. */
 int icr_workspace_set_profile(icr_workspace* ws, int on);
 int icr_profile_read(icr_workspace* ws, float* ms4);
 

@@ -1,7 +1,8 @@
 #!/usr/bin/env python
 """Randomised parity sweep: the CUDA path (through the Python mirror of the C ABI) against the CPU oracle on random shapes,
-partitions, label encodings and parameters.  Not part of the test suite (it runs for minutes); `python tools/fuzz_parity.py
-[iterations] [seed]` on a GPU box.  Exits non-zero on the first mismatch and prints the case's recipe."""
+partitions, label encodings and parameters.  `python tools/fuzz_parity.py [iterations] [seed]` on a GPU box runs for
+minutes and exits non-zero on the first mismatch, printing the case's recipe; tests/test_full_size_configs.py runs a
+seeded, time-boxed slice of the same sweep (`run`) inside the GPU suite."""
 import os
 import sys
 import time
@@ -54,16 +55,24 @@ def random_image(rng, H, W):
     return np.ascontiguousarray(img, dtype=np.float32)
 
 
-def main():
+class Mismatch(AssertionError):
+    pass
+
+
+def run(iters, seed, budget_s=None, log=print):
+    """Runs up to `iters` random cases (or until `budget_s` seconds have passed); returns (cases run, worst relative
+    reward error).  Raises Mismatch with the case's recipe on the first disagreement with the oracle."""
     import torch
     from image_compression_cpp_b200 import reward as icr
     from oracle import oracle as orc
-    iters = int(sys.argv[1]) if len(sys.argv) > 1 else 300
-    seed = int(sys.argv[2]) if len(sys.argv) > 2 else 1
     rng = np.random.default_rng(seed)
     dev = torch.device("cuda:0")
     t0, worst = time.time(), 0.0
+    done = 0
     for it in range(iters):
+        if budget_s is not None and time.time() - t0 > budget_s:
+            break
+        done += 1
         H = int(rng.choice([1, 2, 3, 5, 8, 16, 24, 31, 48, 64, 100, 128, 160]))
         W = int(rng.choice([1, 3, 4, 7, 8, 12, 16, 20, 28, 32, 36, 40, 56, 64, 100, 128, 200, 256, 300]))
         B, S = int(rng.integers(1, 4)), int(rng.choice([1, 1, 2]))
@@ -85,8 +94,7 @@ def main():
             # beyond the C ABI's contract (spread below the bitmap capacity): it must say so; the host layers rank first
             try:
                 icr.compute_rewards_batched(ti, tl, ts, workspace=ws, **kw)
-                print("MISSING ERROR", recipe)
-                sys.exit(1)
+                raise Mismatch(f"MISSING ERROR {recipe}")
             except RuntimeError as e:
                 assert "label spread" in str(e), e
             ranked = np.stack([np.unique(m, return_inverse=True)[1].reshape(H, W) for m in labels]).astype(dtype)
@@ -101,8 +109,7 @@ def main():
         rel = float(np.max(np.abs(got - want) / np.maximum(np.abs(want), 1e-300)))
         worst = max(worst, rel)
         if not ok or rel > 1e-9:
-            print("MISMATCH", recipe, "rel", rel, "tables ok", ok)
-            sys.exit(1)
+            raise Mismatch(f"MISMATCH {recipe} rel {rel} tables ok {ok}")
         # the slices of the same call: a few of them against the oracle's Rule P, and the decoder round trip of map 0
         ws.inputs = (ti, tl, ts)
         swap = bool(rng.integers(0, 2))
@@ -122,21 +129,29 @@ def main():
                 if swap:
                     ref = ref[..., [2, 1, 0, 3]]
                 if not np.array_equal(sl, ref) or keys[v, k] != uniq[k]:
-                    print("SLICE MISMATCH", recipe, "map", v, "segment", int(k))
-                    sys.exit(1)
+                    raise Mismatch(f"SLICE MISMATCH {recipe} map {v} segment {int(k)}")
             f0 += det["K"][v]
         if offh[-1] != bufh.size or len(offh) != f0 + 1:
-            print("SLICE PLAN MISMATCH", recipe)
-            sys.exit(1)
+            raise Mismatch(f"SLICE PLAN MISMATCH {recipe}")
         canvas = ws.reassemble_map(0, buf, off).cpu().numpy()
         want_canvas = orc.chw3_f32_to_rgba(images[0])
         if swap:
             want_canvas = want_canvas[..., [2, 1, 0, 3]]
         if not np.array_equal(canvas, want_canvas):
-            print("DECODER MISMATCH", recipe)
-            sys.exit(1)
+            raise Mismatch(f"DECODER MISMATCH {recipe}")
         ws.close()
-    print(f"fuzz ok: {iters} cases, seed {seed}, worst relative reward error {worst:.2e}, {time.time() - t0:.0f} s")
+    log(f"fuzz ok: {done} cases, seed {seed}, worst relative reward error {worst:.2e}, {time.time() - t0:.0f} s")
+    return done, worst
+
+
+def main():
+    iters = int(sys.argv[1]) if len(sys.argv) > 1 else 300
+    seed = int(sys.argv[2]) if len(sys.argv) > 2 else 1
+    try:
+        run(iters, seed)
+    except Mismatch as e:
+        print(e)
+        sys.exit(1)
 
 
 if __name__ == "__main__":
