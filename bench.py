@@ -386,7 +386,7 @@ def main():
         L.icr_profile_read(ws.handle, kms[i].ctypes.data_as(C.c_void_p))
     L.icr_workspace_set_profile(ws.handle, 0)
     kavg = kms.mean(0).astype(np.float64)
-    names = ["prep_kernel", "narrow_kernel", "estimate_kernel (wide)", "big_kernel"]
+    names = ["prep_kernel", "narrow_kernel", "big_kernel", "reserved"]
     top = int(np.argmax(kavg))
     peak, peak_src = peaks()
     alg_bytes = bytes_per_image(Kmean) * B

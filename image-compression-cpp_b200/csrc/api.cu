@@ -3,6 +3,7 @@
 #include "icr_internal.h"
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -40,6 +41,13 @@ static int cuda_fail(cudaError_t e, const char* what) {
 
 static size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
 
+// Which estimator takes the warp-path work lists.  Both produce the same tables (the GPU suite runs under either);
+// ICR_ESTIMATOR=reg selects the register path of narrow.cu, anything else the shared-memory tile path of estimate.cu.
+static bool use_register_path() {
+    static const int v = [] { const char* e = std::getenv("ICR_ESTIMATOR"); return (e && std::string(e) == "reg") ? 1 : 0; }();
+    return v != 0;
+}
+
 int sm_count() {
     static int cached[64] = {0};
     int dev = 0;
@@ -52,7 +60,7 @@ int sm_count() {
 }
 
 struct Layout { size_t K, status, counts, bboxes, keys, sizes, err, seg_prefix, sched, big_filter, clog2, heads, hslot, chg, slice_map_off,
-                done, list_narrow, list_other, total; };
+                nbig, done, list_a, list_b, list_big, total; };
 
 static Layout layout(int V, int H, int W, int Kmax) {
     Layout l; size_t o = 0;
@@ -71,9 +79,11 @@ static Layout layout(int V, int H, int W, int Kmax) {
     l.hslot = o; o = align_up(o + (size_t)V * head_capacity(H, W) * 4);
     l.chg = o; o = align_up(o + (chg_in_smem(H, W) ? 0 : (size_t)V * (size_t)chg_bytes(H, W)));
     l.slice_map_off = o; o = align_up(o + (size_t)V * 8);
+    l.nbig = o; o = align_up(o + (size_t)V * 4);
     l.done = o; o = align_up(o + (size_t)V * 4);
-    l.list_narrow = o; o = align_up(o + (size_t)V * Kmax * 8);
-    l.list_other = o; o = align_up(o + (size_t)V * Kmax * 8);
+    l.list_a = o; o = align_up(o + (size_t)V * Kmax * 8);
+    l.list_b = o; o = align_up(o + (size_t)V * Kmax * 8);
+    l.list_big = o; o = align_up(o + (size_t)V * Kmax * 8);
     l.total = o;
     return l;
 }
@@ -145,8 +155,8 @@ int icr_workspace_create(icr_workspace** out, int device, int V, int H, int W, i
     t.heads = (uint32_t*)(ws->base + l.heads); t.hslot = (uint32_t*)(ws->base + l.hslot); t.head_cap = head_capacity(H, W);
     t.chg_global = chg_in_smem(H, W) ? nullptr : (uint8_t*)(ws->base + l.chg); t.chg_stride = chg_bytes(H, W);
     t.slice_map_off = (unsigned long long*)(ws->base + l.slice_map_off);
-    t.done = (int32_t*)(ws->base + l.done);
-    t.list_narrow = (uint2*)(ws->base + l.list_narrow); t.list_other = (uint2*)(ws->base + l.list_other);
+    t.nbig = (int32_t*)(ws->base + l.nbig); t.done = (int32_t*)(ws->base + l.done);
+    t.list_a = (uint2*)(ws->base + l.list_a); t.list_b = (uint2*)(ws->base + l.list_b); t.list_big = (uint2*)(ws->base + l.list_big);
     t.list_cap = (int64_t)V * Kmax;
     std::vector<double> tab(CLOG2_N);
     tab[0] = 0.0;
@@ -203,14 +213,13 @@ static int compute_rewards_impl(const float* images, const void* labels, int lab
     }
     ws->dirty = 1;
     if (prof) cudaEventRecord(ws->ev[0], st);
-    ICR_CUDA(launch_prep(labels, label_dtype, t, true, p.L_min, rw, st), "prep");
+    ICR_CUDA(launch_prep(labels, label_dtype, t, use_register_path() ? 2 : 1, p.L_min, rw, st), "prep");
     if (prof) cudaEventRecord(ws->ev[1], st);
-    ICR_CUDA(launch_narrow(t, in, p, rw, st), "narrow");
+    if (use_register_path()) ICR_CUDA(launch_narrow(t, in, p, rw, st), "narrow");
+    else ICR_CUDA(launch_tile(t, in, p, rw, st), "estimate");
     if (prof) cudaEventRecord(ws->ev[2], st);
-    ICR_CUDA(launch_wide(t, in, p, rw, st), "wide");
-    if (prof) cudaEventRecord(ws->ev[3], st);
     ICR_CUDA(launch_big(t, in, p, rw, st), "big_segment");       // also resets the work lists and signals the peers
-    if (prof) cudaEventRecord(ws->ev[4], st);
+    if (prof) { cudaEventRecord(ws->ev[3], st); cudaEventRecord(ws->ev[4], st); }
     ws->dirty = 0;
     return ICR_OK;
 }
@@ -332,7 +341,7 @@ int icr_segment_stats(const void* labels, int label_dtype, int V, int H, int W, 
     ws->in = Inputs{nullptr, labels, label_dtype, 1};
     ws->t.V = V;
     ws->prefix_valid = 0;
-    ICR_CUDA(launch_prep(labels, label_dtype, t, false, 4, RewardArgs{nullptr, nullptr, 1}, st), "prep");
+    ICR_CUDA(launch_prep(labels, label_dtype, t, 0, 4, RewardArgs{nullptr, nullptr, 1}, st), "prep");
     if (compact_out) ICR_CUDA(launch_compact_ids(labels, label_dtype, t, compact_out, st), "compact ids");
     if (K_out) ICR_CUDA(cudaMemcpyAsync(K_out, t.K, (size_t)V * 4, cudaMemcpyDeviceToDevice, st), "copy K");
     if (counts) ICR_CUDA(cudaMemcpyAsync(counts, t.counts, (size_t)V * t.Kmax * 4, cudaMemcpyDeviceToDevice, st), "copy counts");
@@ -401,10 +410,10 @@ int icr_debug_segment(icr_workspace* ws, int v, int k, const icr_params* params,
     if (v < 0 || v >= ws->t.V || k < 0 || k >= ws->Kmax) return fail(ICR_EINVAL, "segment index out of range");
     const EstParams p = widen(params);
     cudaStream_t st = (cudaStream_t)stream;
-    // the three kernels classify the segment on the device (segment_class); exactly one of them acts
+    // both kernels classify the segment on the device (segment_class); exactly one of them acts
     if (!ws->in.images) return fail(ICR_EINVAL, "no batch call has run on this workspace");
-    ICR_CUDA(launch_narrow_debug(ws->t, ws->in, p, v, k, row_costs, filter_id, hist, match, size_out, st), "narrow debug");
-    ICR_CUDA(launch_estimate_debug(ws->t, ws->in, p, v, k, row_costs, filter_id, hist, match, size_out, st), "estimate debug");
+    if (use_register_path()) ICR_CUDA(launch_narrow_debug(ws->t, ws->in, p, v, k, row_costs, filter_id, hist, match, size_out, st), "narrow debug");
+    else ICR_CUDA(launch_estimate_debug(ws->t, ws->in, p, v, k, row_costs, filter_id, hist, match, size_out, st), "estimate debug");
     ICR_CUDA(launch_big_debug(ws->t, ws->in, p, v, k, row_costs, filter_id, hist, match, size_out, st), "big debug");
     return ICR_OK;
 }
@@ -428,7 +437,7 @@ int icr_slices_prepare(const float* images, const void* labels, int label_dtype,
     ws->in = Inputs{images, labels, label_dtype, S};
     ws->t.V = t.V;
     ws->prefix_valid = 0;
-    ICR_CUDA(launch_prep(labels, label_dtype, t, false, 4, RewardArgs{nullptr, nullptr, 1}, (cudaStream_t)stream), "prep");
+    ICR_CUDA(launch_prep(labels, label_dtype, t, 0, 4, RewardArgs{nullptr, nullptr, 1}, (cudaStream_t)stream), "prep");
     return ICR_OK;
 }
 

@@ -369,8 +369,8 @@ __device__ void block_segment(const Src& src, int x0, int y0, int w, int h, int 
     __syncthreads();
 }
 
-// Persistent CTAs pull the segments prep put on the back of list_other (Rule M can fire, or the bbox is wider or larger
-// than the warp paths take), one segment per CTA at a time.  This is always the last kernel of a batch call: whichever
+// Persistent CTAs pull the segments prep put on list_big (Rule M can fire, or the bbox is wider or larger than the
+// register path takes), one segment per CTA at a time.  This is always the last kernel of a batch call: whichever
 // CTA finishes last resets the work lists for the next call and, in a sharded run, tells the peers that this rank's
 // rewards have landed.
 template <typename LT>
@@ -380,12 +380,15 @@ __global__ void __launch_bounds__(BIG_T, 4) big_kernel(Tables t, Inputs in, EstP
     BigDebug none{};
     const int total = t.sched[SC_N_BIG];
     uint8_t* filt = t.big_filter + (int64_t)blockIdx.x * t.H;
+    // Rule W for the maps whose sizes all came from the kernel before: a warp per map
+    for (int v = blockIdx.x * (BIG_T / 32) + (threadIdx.x >> 5); v < t.V; v += gridDim.x * (BIG_T / 32))
+        if (t.status[v] == ST_OK && t.nbig[v] == 0) reward_of_map<false>(t, p, rw.image_sizes, rw.S, rw.rewards, v, threadIdx.x & 31);
     for (;;) {
         if (threadIdx.x == 0) s_next = total > 0 ? atomicAdd(&t.sched[SC_CUR_BIG], 1) : 0;
         __syncthreads();
         const int i = s_next;
         if (i >= total) break;
-        const uint2 e = t.list_other[t.list_cap - 1 - i];
+        const uint2 e = t.list_big[i];
         const int v = (int)e.x, k = (int)e.y;
         const int64_t row = (int64_t)v * t.Kmax + k;
         const int4 bb = t.bboxes[row];
@@ -393,7 +396,7 @@ __global__ void __launch_bounds__(BIG_T, 4) big_kernel(Tables t, Inputs in, EstP
                           (LT)t.keys[row]);
         block_segment(src, bb.x, bb.y, bb.z - bb.x + 1, bb.w - bb.y + 1, 4, p, filt, t.seg_sizes + row, none);
         if (threadIdx.x == 0) {                           // the thread that stored the size
-            s_last = segment_done(t, v, t.K[v]);
+            s_last = segment_done(t, v, t.nbig[v]);
         }
         __syncthreads();
         if (s_last && threadIdx.x < 32) {                 // every size of this map is final: Rule W

@@ -1,11 +1,10 @@
-// estimate (the "wide" kernel): Rules C, P, F, R, H, Z for the segments whose bbox is wider than the register path
-// takes (NARROW_MAX_W < w <= EST_MAX_W) and that need no match statistics, one warp per segment, one launch.
-// The bulk of a batch goes through narrow.cu; this is the shared-memory tile path that any width up to EST_MAX_W fits.
+// estimate (the shared-memory tile path): Rules C, P, F, R, H, Z for every segment whose bbox is at most NARROW_MAX_W
+// pixels wide and that needs no match statistics, one warp per segment, the whole batch in ONE launch.
 // Replaces the reference's 13 stream operations per segment (src/png_size_estimator.cu:505-590),
 // its two nested host loops (src/compute_rewards.cu:125,159) and its RGBA staging kernel (:23-53).
 //
-// Persistent warps pull segments from the work list prep built, one per request with the next request in
-// flight.  A warp owns one segment and walks its bbox in groups of R rows:
+// Persistent warps pull segments from the work lists prep built (widest bboxes first), one per request with the next
+// request in flight.  A warp owns one segment and walks its bbox in groups of R rows:
 //   stage    every lane takes pixels of the group as aligned quads in row-major order (coalesced, all lanes busy
 //            whatever the width).  The quads of group g+1 are requested with cp.async into the warp's raw window
 //            while group g is walked, so their latency is not waited for; on arrival: three f32 planes ->
@@ -19,9 +18,11 @@
 //   residual second walk: predictor = one shared-memory load whose base/step depend on the row's filter
 //            (zero word, left, up, Avg plane, Paeth plane), the four residual bytes of every pixel of the bbox
 //            (zeros included) go to the warp's 4x256 histogram with unconditional ATOMS.POPC.INC.
-//   entropy  branch-free c*log2(c) table look-ups, Rule Z, one f64 store per segment.
+//   entropy  branch-free c*log2(c) table look-ups, Rule Z, one f64 store per segment; the warp that stores the last
+//            size of a label map also computes its reward (Rule W).
 // No residual stream, RGBA plane or compact-id plane is ever written to global memory.  Segments that
-// need Rule M match statistics (chunk >= L_min) or are wider than EST_MAX_W go to the big-segment kernel.
+// need Rule M match statistics (chunk >= L_min) or are wider than NARROW_MAX_W go to the big-segment kernel.
+// narrow.cu holds the other estimator for the same work lists (rows in registers, no tile); api.cu picks one.
 #include "icr_internal.h"
 #include "icr_pixel.cuh"
 #include "icr_reward.cuh"
@@ -29,6 +30,7 @@
 namespace icr {
 
 constexpr int EST_WARPS = 4;          // warps per CTA
+constexpr int EST_MAX_W = NARROW_MAX_W;
 constexpr int MAXSW = 16;             // widest strip one lane walks
 
 // shared-memory budget per warp.  choose_geometry() only returns geometries whose (R+1) row slots of w+2 words fit TILE_CAP;
@@ -326,7 +328,11 @@ __device__ void warp_segment(const float* __restrict__ img, const LT* __restrict
                 const uint32_t ncur = trow[i + 1], nup = urow[i + 1];
                 const uint32_t u_lo = unpack_lo(up), u_hi = unpack_hi(up);
                 const uint32_t pa = avg4(left, up);
+                #ifdef EST_PAETH_FMA
+                const uint32_t pp = __byte_perm(paeth_h2_fma(l_lo, u_lo, ul_lo), paeth_h2_fma(l_hi, u_hi, ul_hi), 0x6420);
+#else
                 const uint32_t pp = __byte_perm(paeth_h2(l_lo, u_lo, ul_lo), paeth_h2(l_hi, u_hi, ul_hi), 0x6420);
+#endif
                 c.none = cost_acc(cur, c.none);
                 c.sub = cost_acc(absdiff4(cur, left), c.sub);
                 c.up = cost_acc(absdiff4(cur, up), c.up);
@@ -431,31 +437,29 @@ __global__ void __launch_bounds__(EST_WARPS * 32, 4) estimate_kernel(Tables t, I
     for (int i = lane; i < 1024; i += 32) sm.hist[i] = 0;
     __syncwarp();
     const int64_t HW = (int64_t)t.H * t.W;
-    const int total = t.sched[SC_N_WIDE];
+    // the four work lists back to back, widest bboxes first: list_a front, list_b front, list_b back, list_a back
+    const int e0 = t.sched[SC_N_W128], e1 = e0 + t.sched[SC_N_W64], e2 = e1 + t.sched[SC_N_W32], total = e2 + t.sched[SC_N_W16];
     const LT* labels = static_cast<const LT*>(in.labels);
     DebugOut none{};
     // One segment per request; the request for the next segment is issued before the current one is worked on.
     int flat = 0;
-    if (lane == 0) flat = next_segment(&t.sched[SC_CUR_WIDE]);
+    if (lane == 0) flat = next_segment(&t.sched[SC_CUR_NARROW]);
     flat = __shfl_sync(0xffffffffu, flat, 0);
     while (flat < total) {
         int fut = 0;
-        if (lane == 0) fut = next_segment(&t.sched[SC_CUR_WIDE]);
-        const uint2 e = __ldg(t.list_other + flat);
+        if (lane == 0) fut = next_segment(&t.sched[SC_CUR_NARROW]);
+        const uint2* slot = flat < e0 ? t.list_a + flat
+                          : flat < e1 ? t.list_b + (flat - e0)
+                          : flat < e2 ? t.list_b + (t.list_cap - 1 - (int64_t)(flat - e1))
+                                      : t.list_a + (t.list_cap - 1 - (int64_t)(flat - e2));
+        const uint2 e = __ldg(slot);
         const int v = (int)e.x, k = (int)e.y;
         const int64_t row = (int64_t)v * t.Kmax + k;
         const int4 bb = __ldg(t.bboxes + row);
         const LT key = (LT)__ldg(t.keys + row);
         const int count = __ldg(t.counts + row);
-        const int K = __ldg(t.K + v);
         warp_segment<LT, false, VEC>(in.images + (int64_t)(v / in.S) * 3 * HW, labels + (int64_t)v * HW, HW, t.W, key, count, bb, sm, p,
                                      t.clog2, t.seg_sizes + row, none);
-        int last = 0;
-        if (lane == 0) last = segment_done(t, v, K);       // lane 0 stored the size
-        if (__shfl_sync(0xffffffffu, last, 0)) {         // every size of this map is final: Rule W
-            __threadfence();
-            reward_of_map<true>(t, p, rw.image_sizes, rw.S, rw.rewards, v, lane);
-        }
         flat = __shfl_sync(0xffffffffu, fut, 0);
     }
 }
@@ -468,7 +472,7 @@ __global__ void __launch_bounds__(32) estimate_debug_kernel(Tables t, Inputs in,
     __syncwarp();
     const int64_t HW = (int64_t)t.H * t.W;
     const int4 bb = t.bboxes[(int64_t)dbg.v * t.Kmax + dbg.k];
-    if (segment_class(bb.z - bb.x + 1, bb.w - bb.y + 1, p.L_min) != CLS_WIDE) return;     // another debug kernel acts
+    if (segment_class(bb.z - bb.x + 1, bb.w - bb.y + 1, p.L_min) != CLS_NARROW) return;     // the big-segment debug kernel acts
     const LT key = (LT)t.keys[(int64_t)dbg.v * t.Kmax + dbg.k];
     double scratch;
     warp_segment<LT, true, VEC>(in.images + (int64_t)(dbg.v / in.S) * 3 * HW, static_cast<const LT*>(in.labels) + (int64_t)dbg.v * HW,
@@ -502,7 +506,7 @@ static cudaError_t launch_est_t(const Tables& t, const Inputs& in, const EstPara
     return cudaGetLastError();
 }
 
-cudaError_t launch_wide(const Tables& t, const Inputs& in, const EstParams& p, const RewardArgs& rw, cudaStream_t st) {
+cudaError_t launch_tile(const Tables& t, const Inputs& in, const EstParams& p, const RewardArgs& rw, cudaStream_t st) {
     const bool vec = vec_ok(t, in);
     if (in.label_dtype == ICR_LABELS_I64) return vec ? launch_est_t<int64_t, true>(t, in, p, rw, st) : launch_est_t<int64_t, false>(t, in, p, rw, st);
     return vec ? launch_est_t<int32_t, true>(t, in, p, rw, st) : launch_est_t<int32_t, false>(t, in, p, rw, st);

@@ -28,14 +28,18 @@ struct Tables {            // device pointers into the workspace, V label maps
     int head_cap;          // run heads a map's list holds (an average run of 8 pixels fits); beyond it prep walks the change bitmap
     uint8_t* chg_global;   // [V, chg_stride] change bitmap of a map when it does not fit shared memory, else NULL
     int64_t chg_stride;
-    // Work lists prep leaves for the estimator kernels: entries {label map v, compact id k}.  list_narrow holds the
-    // segments of the register path (bbox no wider than NARROW_MAX_W): the larger ones from the front, the smaller ones
-    // from the back, so that the kernel starts with the long ones.  list_other: wide segments (shared-memory path) from
-    // the front, Rule M / very large segments (CTA per segment) from the back.
-    uint2* list_narrow;    // [list_cap]
-    uint2* list_other;     // [list_cap]
+    // Work lists prep leaves for the estimator kernels: entries {label map v, compact id k}.  The segments of the register
+    // path (bbox no wider than NARROW_MAX_W, no match statistics) are kept apart by the code variant that will walk them,
+    // widest first: list_a holds bboxes wider than 64 from the front and those up to 16 wide from the back, list_b those of
+    // 33..64 from the front and 17..32 from the back.  The kernel takes them in that order, so the warps of an SM run the
+    // same variant most of the time (its instruction cache holds one variant, not all of them) and the long segments
+    // start first.  list_big: Rule M, wider or very large segments (CTA per segment).
+    uint2* list_a;         // [list_cap]
+    uint2* list_b;         // [list_cap]
+    uint2* list_big;       // [list_cap]
     int64_t list_cap;
-    int32_t* done;         // [V] segments of a map whose size has been written; the writer of the last one computes Rule W
+    int32_t* nbig;         // [V] segments of a map on list_big (prep)
+    int32_t* done;         // [V] big-kernel segments of a map whose size has been written; the writer of the last one computes Rule W
     unsigned long long* slice_map_off;   // [V] byte offset of a map's first slice in the packed slice buffer (slices.cu)
     const double* clog2;   // [CLOG2_N] c*log2(c)
     // multi-GPU gather fused into the reward writer (icr_compute_rewards_gather): the reward of map v also goes to
@@ -59,28 +63,19 @@ struct Inputs {            // the caller's device buffers of the current call
 };
 
 constexpr int CLOG2_N = 4096;
-constexpr int NARROW_MAX_W = 64;  // widest bbox of the register path (two 32-lane chunks per row)
-constexpr int LPT_AREA = 768;     // narrow segments with a larger bbox are handed out first
+constexpr int NARROW_MAX_W = 224; // widest bbox of the warp paths (a one-row group must fit the tile path's shared-memory tile)
 constexpr int BIG_GRID_MAX = 148 * 8;
 
 // t.sched[]: list lengths are written by prep, cursors by the consuming kernels; the tail kernel's last CTA zeroes them
-enum : int { SC_N_LARGE = 0, SC_N_SMALL, SC_N_WIDE, SC_N_BIG, SC_CUR_NARROW, SC_CUR_WIDE, SC_CUR_BIG, SC_TAIL_DONE, SC_PEER_DONE,
-             SC_PREP_DONE, SCHED_N = 16 };
-constexpr int EST_MAX_W = 224;    // widest bbox of the warp path: a one-row group (two row slots) must fit the warp's tile
+enum : int { SC_N_W128 = 0, SC_N_W64, SC_N_W32, SC_N_W16, SC_N_BIG, SC_CUR_NARROW, SC_CUR_BIG, SC_TAIL_DONE, SCHED_N = 8 };
+
+// work list of a narrow segment by bbox width: 0: 65..NARROW_MAX_W, 1: 33..64, 2: 17..32, 3: 1..16
+__host__ __device__ inline int width_class(int w) { return w > 64 ? 0 : (w > 32 ? 1 : (w > 16 ? 2 : 3)); }
 constexpr int EST_MAX_AREA = 1 << 20;
 
 // Segments the warp path leaves to the big-segment kernel: Rule M can fire (chunk = ceil(N/65536) >= L_min,
-// src/png_size_estimator.cu:416-451), or the bbox is wider than 32 register strips, or very large.
-__host__ __device__ inline bool for_big_kernel(int w, int h, int L_min) {
-    if (w <= 0 || h <= 0) return false;
-    long long N = 4ll * w * h;
-    return (N + 65535) / 65536 >= (long long)L_min || w > EST_MAX_W || (long long)w * h > EST_MAX_AREA;
-}
-
-// can a map whose largest bbox has `area` pixels and whose widest bbox has `maxw` columns hold a big-kernel segment?
-__host__ __device__ inline bool map_may_need_big_kernel(int area, int maxw, int L_min) {
-    return (4ll * area + 65535) / 65536 >= (long long)L_min || maxw > EST_MAX_W || (long long)area > EST_MAX_AREA;
-}
+// src/png_size_estimator.cu:416-451), or the bbox is wider than four register chunks, or very large.
+__host__ __device__ inline bool for_big_kernel(int w, int h, int L_min);
 
 struct DebugOut {          // per-segment tables the debug entry fills (device pointers, may be NULL)
     int v, k;
@@ -123,22 +118,24 @@ inline bool chg_in_smem(int H, int W) {
 // what the kernels that write segment sizes need for Rule W: whoever writes the last size of a map computes its reward
 struct RewardArgs { const double* image_sizes; double* rewards; int S; };
 
-// lists = true: build the estimator's work lists (batch path); false: tables only (icr_segment_stats, icr_slices_prepare).
+// lists: 0 = tables only (icr_segment_stats, icr_slices_prepare); 1 = the estimator's work lists with one warp-path list in
+// map order (tile path); 2 = warp-path lists by bbox width class (register path).
 // Maps that cannot be processed get a NaN reward from prep itself when rw.rewards (or the peer vectors) are set.
-cudaError_t launch_prep(const void* labels, int label_dtype, const Tables& t, bool lists, int L_min, const RewardArgs& rw,
+cudaError_t launch_prep(const void* labels, int label_dtype, const Tables& t, int lists, int L_min, const RewardArgs& rw,
                         cudaStream_t st);
 cudaError_t launch_compact_ids(const void* labels, int label_dtype, const Tables& t, int32_t* compact_out, cudaStream_t st);
 cudaError_t launch_seg_prefix(const Tables& t, cudaStream_t st);
+// the two estimators for the warp-path work lists: rows in registers (narrow.cu) or in a shared-memory tile (estimate.cu)
 cudaError_t launch_narrow(const Tables& t, const Inputs& in, const EstParams& p, const RewardArgs& rw, cudaStream_t st);
-cudaError_t launch_wide(const Tables& t, const Inputs& in, const EstParams& p, const RewardArgs& rw, cudaStream_t st);
+cudaError_t launch_tile(const Tables& t, const Inputs& in, const EstParams& p, const RewardArgs& rw, cudaStream_t st);
+cudaError_t launch_estimate_debug(const Tables& t, const Inputs& in, const EstParams& p, int v, int k, uint32_t* row_costs,
+                                  uint8_t* filter_id, uint32_t* hist, unsigned long long* match,
+                                  double* size_out, cudaStream_t st);
 // always the last kernel of a batch call: Rule M segments, then its last CTA resets the work lists and signals the peers
 cudaError_t launch_big(const Tables& t, const Inputs& in, const EstParams& p, const RewardArgs& rw, cudaStream_t st);
 cudaError_t launch_narrow_debug(const Tables& t, const Inputs& in, const EstParams& p, int v, int k, uint32_t* row_costs,
                                 uint8_t* filter_id, uint32_t* hist, unsigned long long* match,
                                 double* size_out, cudaStream_t st);
-cudaError_t launch_estimate_debug(const Tables& t, const Inputs& in, const EstParams& p, int v, int k, uint32_t* row_costs,
-                                  uint8_t* filter_id, uint32_t* hist, unsigned long long* match,
-                                  double* size_out, cudaStream_t st);
 cudaError_t launch_big_debug(const Tables& t, const Inputs& in, const EstParams& p, int v, int k, uint32_t* row_costs,
                              uint8_t* filter_id, uint32_t* hist, unsigned long long* match,
                              double* size_out, cudaStream_t st);
@@ -165,11 +162,14 @@ cudaError_t run_selftest(int* mismatches);
 void count_launch(int n = 1);
 int sm_count();            // multiprocessors of the current device (cached per device)
 
-// which kernel takes a segment with a w x h bbox
-enum : int { CLS_NARROW = 0, CLS_WIDE = 1, CLS_BIG = 2 };
-__host__ __device__ inline int segment_class(int w, int h, int L_min) {
-    if (for_big_kernel(w, h, L_min)) return CLS_BIG;
-    return w > NARROW_MAX_W ? CLS_WIDE : CLS_NARROW;
+__host__ __device__ inline bool for_big_kernel(int w, int h, int L_min) {
+    if (w <= 0 || h <= 0) return false;
+    long long N = 4ll * w * h;
+    return (N + 65535) / 65536 >= (long long)L_min || w > NARROW_MAX_W || (long long)w * h > EST_MAX_AREA;
 }
+
+// which kernel takes a segment with a w x h bbox
+enum : int { CLS_NARROW = 0, CLS_BIG = 1 };
+__host__ __device__ inline int segment_class(int w, int h, int L_min) { return for_big_kernel(w, h, L_min) ? CLS_BIG : CLS_NARROW; }
 
 }  // namespace icr

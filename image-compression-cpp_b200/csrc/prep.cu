@@ -13,7 +13,7 @@
 //   scan B   a thread per head: count += length, bbox min / max as unconditional shared-memory atomics on the rank's row
 //            (the reference does five global atomics per PIXEL, src/segment_stats.cu:37-41)
 //   publish  keys, table rows, and one entry {map, segment} per segment in the work list of the kernel that will take it
-//            (register path large / small, shared-memory path, CTA-per-segment path), appended with one atomic per warp.
+//            (register path by width class, CTA-per-segment path), appended with one atomic per warp.
 // Maps whose run heads overflow the list (average run below 8 pixels) walk the change bitmap instead of the list.
 // The image is not touched here: the estimator masks by comparing raw labels with the segment's key.
 #include "icr_internal.h"
@@ -82,21 +82,26 @@ __device__ __forceinline__ void add_run(const StatsPtr& st, int kc, int n, int x
     }
 }
 
-// append this thread's segment (or nothing) to one of the four work lists: one atomic per warp and list
+// append this thread's segment (or nothing) to one of the five work lists (0..3: register path by width class, 4: big-
+// segment kernel): one atomic per warp and list
 __device__ __forceinline__ void append_segment(const Tables& t, bool have, int cat, int v, int k) {
     const int lane = threadIdx.x & 31;
     const uint32_t ltm = (1u << lane) - 1u;
 #pragma unroll
-    for (int c = 0; c < 4; ++c) {
+    for (int c = 0; c < 5; ++c) {
         const uint32_t m = __ballot_sync(0xffffffffu, have && cat == c);
         if (!m) continue;
         int base = 0;
-        if (lane == __ffs(m) - 1) base = atomicAdd(&t.sched[SC_N_LARGE + c], __popc(m));
+        if (lane == __ffs(m) - 1) base = atomicAdd(&t.sched[SC_N_W128 + c], __popc(m));
         base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
         if (have && cat == c) {
             const int64_t pos = base + __popc(m & ltm);
-            uint2* list = c < 2 ? t.list_narrow : t.list_other;
-            list[(c & 1) ? t.list_cap - 1 - pos : pos] = make_uint2((uint32_t)v, (uint32_t)k);
+            const uint2 e = make_uint2((uint32_t)v, (uint32_t)k);
+            if (c == 0) t.list_a[pos] = e;
+            else if (c == 1) t.list_b[pos] = e;
+            else if (c == 2) t.list_b[t.list_cap - 1 - pos] = e;
+            else if (c == 3) t.list_a[t.list_cap - 1 - pos] = e;
+            else t.list_big[pos] = e;
         }
     }
 }
@@ -108,7 +113,7 @@ __global__ void __launch_bounds__(PREP_T, 4) prep_kernel(const LT* __restrict__ 
     __shared__ long long red_lo[PREP_W], red_hi[PREP_W];
     __shared__ uint32_t warp_tot[PREP_W];
     __shared__ long long s_min;
-    __shared__ int s_bad;
+    __shared__ int s_bad, s_nbig;
 
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int H = t.H, W = t.W;
@@ -131,30 +136,46 @@ __global__ void __launch_bounds__(PREP_T, 4) prep_kernel(const LT* __restrict__ 
         uint32_t* hslot = t.hslot + (int64_t)v * t.head_cap;
 
         for (int i = tid; i < cap_words; i += PREP_T) bitmap[i] = 0;
+        if (tid == 0) s_nbig = 0;
         for (uint32_t g = ngroups + tid; g < nwords * 4u; g += PREP_T) chgb[g] = 0;     // padding bits of the last word
 
         // ---- mark: one bit per pixel, set at run heads
         if (VEC) {
-            // W % 8 == 0: a group of 8 labels lies in one row and is 32 (64) bytes aligned
-            LT cur[8], nxt[8];
-            LT pv = 0, npv = 0;
-            uint32_t g = tid;
-            int y0, x;
-            divw(g * 8u, y0, x);
-            const int stepx = (int)((PREP_T * 8u) % (uint32_t)W);
-            if (g < ngroups) { load8<LT>(lab + g * 8u, nxt); npv = x ? __ldg(lab + g * 8u - 1) : (LT)0; }
-            for (; g < ngroups; g += PREP_T) {
+            // W % 8 == 0: a group of 8 labels lies in one row and is 32 (64) bytes aligned.  A thread takes NG groups per
+            // trip and asks for the next trip's labels before it looks at this trip's: (2 * NG) x 32 bytes in flight
+            constexpr int NG = sizeof(LT) == 4 ? 2 : 1;
+            LT cur[NG][8], nxt[NG][8], pv[NG], npv[NG];
+            int x[NG];
+            const int stepx = (int)((PREP_T * NG * 8u) % (uint32_t)W);
 #pragma unroll
-                for (int i = 0; i < 8; ++i) cur[i] = nxt[i];
-                pv = npv;
-                const bool rowstart = x == 0;
-                x += stepx; if (x >= W) x -= W;
-                const uint32_t gn = g + PREP_T;
-                if (gn < ngroups) { load8<LT>(lab + gn * 8u, nxt); npv = x ? __ldg(lab + gn * 8u - 1) : (LT)0; }
-                uint32_t m = (rowstart || cur[0] != pv) ? 1u : 0u;
+            for (int j = 0; j < NG; ++j) {
+                const uint32_t g = tid + j * PREP_T;
+                int y0;
+                divw(g * 8u, y0, x[j]);
+                npv[j] = 0;
+                if (g < ngroups) { load8<LT>(lab + g * 8u, nxt[j]); if (x[j]) npv[j] = __ldg(lab + g * 8u - 1); }
+            }
+            for (uint32_t g0 = tid; g0 < ngroups; g0 += PREP_T * NG) {
+                bool rowstart[NG];
 #pragma unroll
-                for (int i = 1; i < 8; ++i) m |= (cur[i] != cur[i - 1]) ? (1u << i) : 0u;
-                chgb[g] = (uint8_t)m;
+                for (int j = 0; j < NG; ++j) {
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) cur[j][i] = nxt[j][i];
+                    pv[j] = npv[j];
+                    rowstart[j] = x[j] == 0;
+                    x[j] += stepx; if (x[j] >= W) x[j] -= W;
+                    const uint32_t gn = g0 + (j + NG) * PREP_T;
+                    if (gn < ngroups) { load8<LT>(lab + gn * 8u, nxt[j]); npv[j] = x[j] ? __ldg(lab + gn * 8u - 1) : (LT)0; }
+                }
+#pragma unroll
+                for (int j = 0; j < NG; ++j) {
+                    const uint32_t g = g0 + j * PREP_T;
+                    if (g >= ngroups) break;
+                    uint32_t m = (rowstart[j] || cur[j][0] != pv[j]) ? 1u : 0u;
+#pragma unroll
+                    for (int i = 1; i < 8; ++i) m |= (cur[j][i] != cur[j][i - 1]) ? (1u << i) : 0u;
+                    chgb[g] = (uint8_t)m;
+                }
             }
         } else {
             for (uint32_t g = tid; g < ngroups; g += PREP_T) {
@@ -198,7 +219,18 @@ __global__ void __launch_bounds__(PREP_T, 4) prep_kernel(const LT* __restrict__ 
             return idx;
         };
         if (listed) {
-            for (uint32_t i = tid; i < nheads; i += PREP_T) hslot[i] = mark(__ldg(lab + heads[i]));
+            // four heads per thread and trip: the positions, then the labels, are asked for together (two memory round trips
+            // per trip instead of two per head)
+            for (uint32_t i0 = tid; i0 < nheads; i0 += 4 * PREP_T) {
+                uint32_t p[4];
+                LT l[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) { const uint32_t i = i0 + j * PREP_T; p[j] = i < nheads ? heads[i] : 0xffffffffu; }
+#pragma unroll
+                for (int j = 0; j < 4; ++j) l[j] = p[j] != 0xffffffffu ? __ldg(lab + p[j]) : (LT)0;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) if (p[j] != 0xffffffffu) hslot[i0 + j * PREP_T] = mark(l[j]);
+            }
         } else {
             for (uint32_t w = tid; w < nwords; w += PREP_T) {
                 uint32_t bits = chgw[w];
@@ -274,13 +306,23 @@ __global__ void __launch_bounds__(PREP_T, 4) prep_kernel(const LT* __restrict__ 
             }
             __syncthreads();
             if (listed) {
-                for (uint32_t i = tid; i < nheads; i += PREP_T) {
-                    const uint32_t p = heads[i];
-                    const uint32_t nx = i + 1 < nheads ? heads[i + 1] : HW;      // every row start is a head: the run ends in its row
-                    int y, x;
-                    divw(p, y, x);
-                    const int kc = (int)rank_slot(hslot[i]);
-                    if (in_smem) add_run<true>(st, kc, (int)(nx - p), x, y); else add_run<false>(st, kc, (int)(nx - p), x, y);
+                for (uint32_t i0 = tid; i0 < nheads; i0 += 4 * PREP_T) {
+                    uint32_t p[4], nx[4], sl[4];
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const uint32_t i = i0 + j * PREP_T;
+                        p[j] = i < nheads ? heads[i] : 0xffffffffu;
+                        nx[j] = i + 1 < nheads ? heads[i + 1] : HW;      // every row start is a head: the run ends in its row
+                        sl[j] = i < nheads ? hslot[i] : 0u;
+                    }
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        if (p[j] == 0xffffffffu) continue;
+                        int y, x;
+                        divw(p[j], y, x);
+                        const int kc = (int)rank_slot(sl[j]);
+                        if (in_smem) add_run<true>(st, kc, (int)(nx[j] - p[j]), x, y); else add_run<false>(st, kc, (int)(nx[j] - p[j]), x, y);
+                    }
                 }
             } else {
                 for (uint32_t w = tid; w < nwords; w += PREP_T) {
@@ -319,15 +361,20 @@ __global__ void __launch_bounds__(PREP_T, 4) prep_kernel(const LT* __restrict__ 
                 }
                 if (lists) {
                     const int bw = bb.z - bb.x + 1, bh = bb.w - bb.y + 1;
-                    const int cls = segment_class(bw, bh, L_min);
-                    const int cat = cls == CLS_NARROW ? ((int64_t)bw * bh > LPT_AREA ? 0 : 1) : (cls == CLS_WIDE ? 2 : 3);
+                    // lists = 1: one warp-path list in map order (neighbouring segments are walked at about the same time, so
+                    // the sectors and label rows they share are still in the L2); lists = 2: by width class
+                    const int cat = segment_class(bw, bh, L_min) == CLS_NARROW ? (lists == 2 ? width_class(bw) : 0) : 4;
                     append_segment(t, have, cat, v, k);
+                    const uint32_t bigs = __ballot_sync(0xffffffffu, have && cat == 4);
+                    if (lane == 0 && bigs) atomicAdd(&s_nbig, __popc(bigs));
                 }
             }
         }
 
         // ---- publish
+        __syncthreads();
         if (tid == 0) {
+            t.nbig[v] = bad ? 0 : s_nbig;
             t.K[v] = bad == ST_LABEL_RANGE ? 0 : K;
             t.status[v] = bad;
             t.done[v] = 0;
@@ -342,7 +389,7 @@ __global__ void __launch_bounds__(PREP_T, 4) prep_kernel(const LT* __restrict__ 
 }
 
 template <typename LT, bool VEC, bool CHG_SMEM>
-static cudaError_t launch_t(const void* labels, const Tables& t, bool lists, int L_min, const RewardArgs& rw, cudaStream_t st) {
+static cudaError_t launch_t(const void* labels, const Tables& t, int lists, int L_min, const RewardArgs& rw, cudaStream_t st) {
     const int cap_words = (int)(label_capacity(t.H, t.W) / 32);
     const int64_t nwords = chg_bytes(t.H, t.W) / 4;
     const int64_t un_words = CHG_SMEM ? (nwords > cap_words ? nwords : cap_words) : cap_words;
@@ -356,20 +403,20 @@ static cudaError_t launch_t(const void* labels, const Tables& t, bool lists, int
     if (e != cudaSuccess) return e;
     const int resident = sm_count() * (per < 1 ? 1 : per);
     const int grid = t.V < resident ? t.V : resident;                   // persistent beyond one wave: CTAs stride over the maps
-    k<<<grid, PREP_T, smem, st>>>(static_cast<const LT*>(labels), t, cap_words, ks_cap, lists ? 1 : 0, L_min, rw);
+    k<<<grid, PREP_T, smem, st>>>(static_cast<const LT*>(labels), t, cap_words, ks_cap, lists, L_min, rw);
     count_launch();
     return cudaGetLastError();
 }
 
 template <typename LT>
-static cudaError_t launch_lt(const void* labels, const Tables& t, bool lists, int L_min, const RewardArgs& rw, cudaStream_t st) {
+static cudaError_t launch_lt(const void* labels, const Tables& t, int lists, int L_min, const RewardArgs& rw, cudaStream_t st) {
     const bool vec = t.W % 8 == 0 && (uintptr_t)labels % 16 == 0;
     const bool sm = t.chg_global == nullptr;
     if (vec) return sm ? launch_t<LT, true, true>(labels, t, lists, L_min, rw, st) : launch_t<LT, true, false>(labels, t, lists, L_min, rw, st);
     return sm ? launch_t<LT, false, true>(labels, t, lists, L_min, rw, st) : launch_t<LT, false, false>(labels, t, lists, L_min, rw, st);
 }
 
-cudaError_t launch_prep(const void* labels, int label_dtype, const Tables& t, bool lists, int L_min, const RewardArgs& rw,
+cudaError_t launch_prep(const void* labels, int label_dtype, const Tables& t, int lists, int L_min, const RewardArgs& rw,
                         cudaStream_t st) {
     if (label_dtype == ICR_LABELS_I64) return launch_lt<int64_t>(labels, t, lists, L_min, rw, st);
     return launch_lt<int32_t>(labels, t, lists, L_min, rw, st);

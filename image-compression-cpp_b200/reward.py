@@ -13,7 +13,7 @@ import os
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libicr_b200.so")
+LIB_PATH = os.environ.get("ICR_LIB") or os.path.join(_HERE, "libicr_b200.so")       # ICR_LIB: an experimental build (tools/)
 _LIB = None
 
 ICR_LABELS_I32, ICR_LABELS_I64 = 0, 1

@@ -74,7 +74,7 @@ def run(name, images, labels, sizes, pool_reps, steps=10):
     alg = B * (H * W * px_bytes + S * (np.mean(K) * 28 + 16))
     print(json.dumps({"config": name, "images": B, "label_maps": B * S, "H": H, "W": W, "mean_K": float(np.mean(K)),
                       "ms_per_step_kernels": ms, "images_per_sec": B / (ms * 1e-3), "rewards_per_sec": B * S / (ms * 1e-3),
-                      "kernel_ms": {"prep": float(k[0]), "narrow": float(k[1]), "wide": float(k[2]), "big": float(k[3])},
+                      "kernel_ms": {"prep": float(k[0]), "narrow": float(k[1]), "big": float(k[2])},
                       "algorithmic_GBps": alg / (ms * 1e-3) / 1e9, "max_rel_err_vs_oracle": err}))
     assert err < 1e-5, err
     # the row after the path: every slice of the batch into one packed buffer (plan + emit), tables already in place
