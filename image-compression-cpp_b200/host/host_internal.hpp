@@ -22,7 +22,9 @@ struct WsHolder {
     ~WsHolder() { if (ws) icr_workspace_destroy(ws); }
 };
 WsHolder& workspace_for(int device, int V, int H, int W, int Kmax);       // reward_host.cpp
-constexpr int KMAX_FIRST = 2048;   // table rows per label map to start with; grown to H*W on demand
+constexpr int KMAX_FIRST = 2048;   // table rows per label map to start with; grown on demand (plan_retry)
+torch::Tensor rank_labels(const torch::Tensor& labs_vhw);                                      // reward_host.cpp
+bool plan_retry(int status_bits, int max_segments, int64_t HW, int& Kmax, bool& rank);        // reward_host.cpp
 
 // extern "C" test hooks report exceptions through these (reward_host.cpp)
 void set_hook_error(const std::string& s);

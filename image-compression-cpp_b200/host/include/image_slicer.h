@@ -24,6 +24,13 @@ struct SliceBatch {
 // RGB planes, the cv::Mat layout of src/compress.cpp:145 -- instead of (c0,c1,c2,255).
 SliceBatch slice_images_batched(const torch::Tensor& images_bchw_f32, const torch::Tensor& labels, bool swap_rb = false);
 
+// slice_image of include/image_slicer.h:6 / src/image_slicer.cpp:48-74 for ONE label VALUE: the bbox crop of the image with
+// the pixels outside the label zeroed, u8 [h,w,4] = (c0,c1,c2,255) inside / (0,0,0,0) outside, on the input's device.
+// input: f32 [3,H,W] or [1,3,H,W] CUDA; mask: integer [H,W] CUDA.  out_box = {x, y, width, height} (cv::Rect order).
+// A label that does not occur returns an empty tensor and leaves out_box alone, as the reference returns cv::Mat().
+struct SliceBox { int x = 0, y = 0, width = 0, height = 0; };
+torch::Tensor slice_image(const torch::Tensor& input_chw_f32, const torch::Tensor& mask, int64_t label, SliceBox& out_box);
+
 // write_slices of src/image_slicer.cpp:81-130: output_path/file_directory_name/slice_<label>.png for every label present
 // plus metadata.bin; records are in ascending label order.  input: f32 [3,H,W] or [1,3,H,W] CUDA, channel planes in the
 // order the PNG should store them (R,G,B); mask: integer [H,W] CUDA.  Returns false when a file could not be written.

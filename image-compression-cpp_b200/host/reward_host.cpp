@@ -61,18 +61,7 @@ WsHolder& workspace_for(int device, int V, int H, int W, int Kmax) {
 
 }  // namespace icrh
 
-namespace {
-
-using icrh::KMAX_FIRST;
-
-
-icr_params make_params(int32_t min_pixels, int L_min, float beta, float token, float gamma, double overhead, bool adaptive,
-                       double lambda) {
-    icr_params p;
-    p.min_pixels = min_pixels; p.L_min = L_min; p.beta = beta; p.b_match_token = token; p.gamma = gamma;
-    p.overhead_base = overhead; p.adaptive_filter = adaptive ? 1 : 0; p.lambda = lambda;
-    return p;
-}
+namespace icrh {
 
 // labels whose value spread defeats the presence bitmap: the reference accepts any integers (it sorts,
 // src/compute_rewards.cu:131-134), so fall back to ranking them with at::_unique per map and rerun on the ranks
@@ -83,6 +72,36 @@ torch::Tensor rank_labels(const torch::Tensor& labs_vhw) {
         out[v].copy_(inv.view({labs_vhw.size(1), labs_vhw.size(2)}));
     }
     return out;
+}
+
+// What to change before the next attempt after icr_check_detail reported data the fast path could not take: more table
+// rows when a map held more segments than Kmax (as many as the largest such map needs, not H*W), ranked labels when a
+// map's label spread exceeded the bitmap.  Returns false when neither applies (give up).
+bool plan_retry(int status_bits, int max_segments, int64_t HW, int& Kmax, bool& rank) {
+    bool changed = false;
+    if ((status_bits & 2) && Kmax < HW) {
+        int64_t want = std::max<int64_t>(max_segments, 2 * (int64_t)Kmax);
+        Kmax = (int)std::min<int64_t>(HW, want);
+        changed = true;
+    }
+    if ((status_bits & 1) && !rank) { rank = true; changed = true; }
+    return changed;
+}
+
+}  // namespace icrh
+
+namespace {
+
+using icrh::KMAX_FIRST;
+using icrh::rank_labels;
+
+
+icr_params make_params(int32_t min_pixels, int L_min, float beta, float token, float gamma, double overhead, bool adaptive,
+                       double lambda) {
+    icr_params p;
+    p.min_pixels = min_pixels; p.L_min = L_min; p.beta = beta; p.b_match_token = token; p.gamma = gamma;
+    p.overhead_base = overhead; p.adaptive_filter = adaptive ? 1 : 0; p.lambda = lambda;
+    return p;
 }
 
 torch::Tensor rewards_impl(const torch::Tensor& images_bchw_f32, const torch::Tensor& labels, const torch::Tensor& image_sizes,
@@ -111,20 +130,21 @@ torch::Tensor rewards_impl(const torch::Tensor& images_bchw_f32, const torch::Te
     const icr_stream st = current_stream();
 
     int Kmax = (int)std::min<int64_t>(H * W, KMAX_FIRST);
-    for (int attempt = 0; attempt < 3; ++attempt) {
+    bool rank = false, ranked = false;
+    for (int attempt = 0; attempt < 4; ++attempt) {
+        if (rank && !ranked) { labs = rank_labels(labs.view({(int64_t)V, H, W})).view(labs.sizes()); ranked = true; }
         WsHolder& h = workspace_for(dev.index(), V, (int)H, (int)W, Kmax);
         const int rc = icr_compute_rewards(images.data_ptr<float>(), labs.data_ptr(), label_code(labs), sizes.data_ptr<double>(),
                                            (int)B, (int)S, (int)H, (int)W, &prm, rewards.data_ptr<double>(), h.ws, st);
         if (rc == ICR_ECUDA) throw_runtime();
         TORCH_CHECK(rc == ICR_OK, icr_last_error());
         // the reference synchronises inside this call too (one blocking D2H per image, src/compute_rewards.cu:152); here it is
-        // one 8-byte read per batch, which also reports label maps the fast path could not take
-        int first_bad = -1;
-        const int chk = icr_check(h.ws, st, &first_bad);
+        // one 16-byte read per batch, which also tells why a label map could not be taken by the fast path
+        int bits = 0, maxk = 0;
+        const int chk = icr_check_detail(h.ws, st, nullptr, &bits, &maxk);
         if (chk == ICR_OK) return rewards;
         if (chk == ICR_ECUDA) throw_runtime();
-        if (h.Kmax < H * W) Kmax = (int)(H * W);                     // more segments than table rows: grow once
-        else labs = rank_labels(labs.view({(int64_t)V, H, W})).view(labs.sizes());      // spread beyond the bitmap: rank first
+        if (!icrh::plan_retry(bits, maxk, H * W, Kmax, rank)) break;
     }
     TORCH_CHECK(false, "compute_rewards_batched: ", icr_last_error());
 }
@@ -271,7 +291,9 @@ torch::Tensor EMABaseline::run(const torch::Tensor& rewards, const torch::Tensor
     if (rc != ICR_OK) throw_runtime();
     if (adv) *adv = a.view(rewards.sizes());
     initialized = true;
-    value = state_[0];
+    // a fresh tensor per update, as the reference's update() produces (include/ema_baseline.hpp:15-19): a caller that keeps
+    // last step's baseline must not see it change (the mean is computed in float64 whatever the rewards' dtype)
+    value = state_[0].clone();
     return value;
 }
 
@@ -375,6 +397,20 @@ int icrh_ema_step(const double* rewards_dev, int n, int device, double momentum,
         }
         state_io[0] = v.item<double>();
         state_io[1] = b.initialized ? 1.0 : 0.0;
+    });
+}
+
+// two updates in a row; returns in values_out the baseline tensor of the FIRST update read after the second one, and the
+// second one's: a caller that keeps last step's baseline must still see last step's number (include/ema_baseline.hpp:15-19)
+int icrh_ema_two_steps(const double* r1_dev, const double* r2_dev, int n, int device, double* values_out) {
+    return guarded([&] {
+        c10::cuda::CUDAGuard g(device);
+        auto f64 = torch::TensorOptions().dtype(torch::kFloat64).device(torch::Device(torch::kCUDA, device));
+        EMABaseline b(0.9);
+        const torch::Tensor v1 = b.update(torch::from_blob((void*)r1_dev, {n}, f64));
+        const torch::Tensor v2 = b.update(torch::from_blob((void*)r2_dev, {n}, f64));
+        values_out[0] = v1.item<double>();
+        values_out[1] = v2.item<double>();
     });
 }
 

@@ -5,6 +5,7 @@
 //   reassemble                                       src/reassemble.cpp:30-120
 // The device cuts every slice of the batch in one pass and pastes on the decoder side; this file moves bytes, encodes
 // and decodes the PNG container (zlib, host threads) and writes files.
+#include <ATen/ops/_unique.h>
 #include <c10/cuda/CUDAGuard.h>
 
 #include <algorithm>
@@ -109,12 +110,16 @@ SliceBatch slice_images_batched(const torch::Tensor& images_bchw_f32, const torc
     const int64_t V = B * S;
     const icr_stream st = current_stream();
     int Kmax = (int)std::min<int64_t>(H * W, icrh::KMAX_FIRST);
+    bool rank = false, ranked = false;
+    torch::Tensor raw_labs = labs;                               // keys are reported in the caller's label values
     WsHolder* hp = nullptr;
-    for (;;) {                                                   // more segments than table rows: grow the tables once, to H*W rows
+    for (int attempt = 0;; ++attempt) {                          // grown tables / ranked labels, as compute_rewards_batched does
+        if (rank && !ranked) { labs = icrh::rank_labels(labs.view({V, H, W})).view(labs.sizes()); ranked = true; }
         hp = &icrh::workspace_for(img.device().index(), (int)V, (int)H, (int)W, Kmax);
         check_rc(icr_slices_prepare(img.data_ptr<float>(), labs.data_ptr(), label_code(labs), (int)B, (int)S, (int)H, (int)W, hp->ws, st));
-        const int rc = icr_check(hp->ws, st, nullptr);
-        if (rc == ICR_EDATA && (int64_t)hp->Kmax < H * W) { Kmax = (int)(H * W); continue; }
+        int bits = 0, maxk = 0;
+        const int rc = icr_check_detail(hp->ws, st, nullptr, &bits, &maxk);
+        if (rc == ICR_EDATA && attempt < 3 && icrh::plan_retry(bits, maxk, H * W, Kmax, rank)) continue;
         check_rc(rc);
         break;
     }
@@ -128,6 +133,13 @@ SliceBatch slice_images_batched(const torch::Tensor& images_bchw_f32, const torc
     const int64_t kcap = std::max<int64_t>(out.K.max().item<int>(), 1);          // rows in use: the tables are H*W rows wide
     out.bboxes = torch::from_blob((void*)pb, {V, (int64_t)km, 4}, i32).slice(1, 0, kcap).clone();
     out.keys = torch::from_blob((void*)pk, {V, (int64_t)km}, i64).slice(1, 0, kcap).clone();
+    if (ranked) {        // the tables hold ranks: report the caller's label values, ascending (what the ranks index)
+        const torch::Tensor raw = raw_labs.view({V, H * W});
+        for (int64_t v = 0; v < V; ++v) {
+            const torch::Tensor uniq = std::get<0>(at::_unique(raw[v], /*sorted=*/true, /*return_inverse=*/false)).to(torch::kInt64);
+            out.keys[v].slice(0, 0, uniq.numel()).copy_(uniq);
+        }
+    }
     const int64_t nseg_cap = out.K.sum().item<int64_t>() + 1;
     torch::Tensor offsets = torch::zeros({nseg_cap}, i64);
     torch::Tensor summary = torch::zeros({2}, i64);
@@ -142,6 +154,24 @@ SliceBatch slice_images_batched(const torch::Tensor& images_bchw_f32, const torc
     out.bytes = out.bytes.slice(0, 0, nbytes);
     out.offsets = offsets;
     return out;
+}
+
+torch::Tensor slice_image(const torch::Tensor& input_chw_f32, const torch::Tensor& mask, int64_t label, SliceBox& out_box) {
+    TORCH_CHECK(input_chw_f32.dim() == 3 || (input_chw_f32.dim() == 4 && input_chw_f32.size(0) == 1), "input must be [3,H,W] or [1,3,H,W]");
+    TORCH_CHECK(mask.dim() == 2, "mask must be [H,W]");
+    const torch::Tensor img = input_chw_f32.dim() == 3 ? input_chw_f32.unsqueeze(0) : input_chw_f32;
+    // the label pass of the whole map (Rules L, S) and its slices are one device pass; the one asked for is picked out
+    const SliceBatch sb = slice_images_batched(img, mask.unsqueeze(0), false);
+    const int K = sb.K.cpu()[0].item<int>();
+    const torch::Tensor keys = sb.keys[0].slice(0, 0, K).cpu();
+    const int64_t* pk = keys.data_ptr<int64_t>();
+    const int64_t* hit = std::lower_bound(pk, pk + K, label);           // keys ascend (Rule L)
+    if (hit == pk + K || *hit != label) return torch::Tensor();        // :55-57
+    const int64_t k = hit - pk;
+    const torch::Tensor bb = sb.bboxes[0][k].cpu(), off = sb.offsets.slice(0, k, k + 2).cpu();
+    const int x0 = bb[0].item<int>(), y0 = bb[1].item<int>(), w = bb[2].item<int>() - x0 + 1, h = bb[3].item<int>() - y0 + 1;
+    out_box.x = x0; out_box.y = y0; out_box.width = w; out_box.height = h;     // :68-71
+    return sb.bytes.slice(0, off[0].item<int64_t>(), off[1].item<int64_t>()).view({h, w, 4}).clone();
 }
 
 bool write_slices(const torch::Tensor& input_chw_f32, const torch::Tensor& mask, const std::filesystem::path& output_path,
@@ -236,6 +266,28 @@ int icrh_write_slices(const float* image_dev, const void* mask_dev, int mask_i64
         ok = write_slices(img, mask, output_path, dir_name) ? 1 : 0;
     });
     return rc ? rc : (ok ? 0 : 4);
+}
+
+// slice_image for one label value: box_out = {x, y, w, h}; the slice goes to slice_out_dev (capacity bytes).  Returns 0,
+// or -1 when the label does not occur (empty result, as the reference's empty cv::Mat).
+int icrh_slice_image(const float* image_dev, const void* mask_dev, int mask_i64, int H, int W, int device, long long label,
+                     int32_t* box_out, uint8_t* slice_out_dev, long long capacity) {
+    int found = 0;
+    const int rc = guarded([&] {
+        c10::cuda::CUDAGuard g(device);
+        auto dev = torch::Device(torch::kCUDA, device);
+        auto img = torch::from_blob((void*)image_dev, {3, H, W}, torch::TensorOptions().dtype(torch::kFloat32).device(dev));
+        auto mask = torch::from_blob((void*)mask_dev, {H, W}, torch::TensorOptions().dtype(mask_i64 ? torch::kInt64 : torch::kInt32).device(dev));
+        SliceBox box;
+        const torch::Tensor sl = slice_image(img, mask, label, box);
+        if (!sl.defined()) return;
+        found = 1;
+        box_out[0] = box.x; box_out[1] = box.y; box_out[2] = box.width; box_out[3] = box.height;
+        TORCH_CHECK(sl.numel() <= capacity, "slice buffer too small");
+        torch::from_blob((void*)slice_out_dev, {sl.numel()}, torch::TensorOptions().dtype(torch::kUInt8).device(dev)).copy_(sl.reshape({-1}));
+        torch::cuda::synchronize(device);
+    });
+    return rc ? rc : (found ? 0 : -1);
 }
 
 int icrh_reassemble(const char* image_path, const char* out_filename, int device, uint8_t* canvas_out_dev, int H, int W) {

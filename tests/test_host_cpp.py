@@ -223,3 +223,57 @@ def test_cpp_write_slices_files_and_reassemble_round_trip(host, orc, dev, tmp_pa
     assert np.array_equal(canvas.cpu().numpy(), rgba)
     assert host.icrh_reassemble(str(tmp_path / "nothing").encode(), None, 0, _p(canvas), H, W) == 2
     assert b"Cannot open metadata file" in host.icrh_last_error()
+
+
+@pytest.mark.gpu
+def test_cpp_slice_image_by_label_value(host, orc, dev):
+    """slice_image(input, mask, label, out_box) of include/image_slicer.h:6 / src/image_slicer.cpp:48-74 for one label VALUE:
+    bbox + masked crop, bit for bit against the slicer restatement; a label that does not occur gives the empty result."""
+    from oracle import slices_oracle as so
+    H, W = 72, 100
+    image = synth.image_f32_chw(3, H, W, 31)
+    mask = (synth.bfs_partition(H, W, 9, seed=4) * 13 - 20).astype(np.int64)
+    ti, tm = _dev(image, mask)
+    rgba = orc.chw3_f32_to_rgba(image)
+    out = torch.zeros(H * W * 4, dtype=torch.uint8, device="cuda")
+    box = np.zeros(4, np.int32)
+    for label in np.unique(mask)[[0, 3, -1]]:
+        rc = host.icrh_slice_image(_p(ti), _p(tm), 1, H, W, 0, C.c_longlong(int(label)), box.ctypes.data_as(C.c_void_p), _p(out),
+                                   C.c_longlong(out.numel()))
+        assert rc == 0, host.icrh_last_error()
+        sl, (x, y, w, h) = so.slice_image(rgba, mask, int(label))
+        assert box.tolist() == [x, y, w, h]
+        assert np.array_equal(out[:w * h * 4].cpu().numpy().reshape(h, w, 4), sl)
+    rc = host.icrh_slice_image(_p(ti), _p(tm), 1, H, W, 0, C.c_longlong(12345), box.ctypes.data_as(C.c_void_p), _p(out),
+                               C.c_longlong(out.numel()))
+    assert rc == -1
+
+
+@pytest.mark.gpu
+def test_cpp_ema_value_is_a_fresh_tensor_per_update(host, dev):
+    """include/ema_baseline.hpp:15-19 returns a new tensor each step: last step's baseline must not change under a caller
+    that kept it."""
+    r1, r2 = np.full(8, 2.0), np.full(8, 10.0)
+    t1, t2 = _dev(r1, r2)
+    vals = np.zeros(2)
+    assert host.icrh_ema_two_steps(_p(t1), _p(t2), 8, 0, vals.ctypes.data_as(C.c_void_p)) == 0, host.icrh_last_error()
+    assert vals[0] == 2.0 and abs(vals[1] - (0.9 * 2.0 + 0.1 * 10.0)) < 1e-12
+
+
+@pytest.mark.gpu
+def test_cpp_slices_with_labels_beyond_the_bitmap_are_ranked(host, orc, dev, tmp_path):
+    """write_slices on a mask whose label spread defeats the presence bitmap: ranked on the fly, file names and sidecar
+    still carry the caller's label values (int32 range, as the reference's SliceMetadata::label)."""
+    from oracle import slices_oracle as so
+    H, W = 40, 48
+    image = synth.image_f32_chw(2, H, W, 5)
+    mask = synth.grid_partition(H, W, 20, 16).astype(np.int64)
+    mask[mask == mask.max()] = (1 << 30) + 7
+    ti, tm = _dev(image, mask)
+    assert host.icrh_write_slices(_p(ti), _p(tm), 1, H, W, 0, str(tmp_path).encode(), b"wide") == 0, host.icrh_last_error()
+    rgba = orc.chw3_f32_to_rgba(image)
+    recs = []                       # what src/image_slicer.cpp:96-117 records: the labels that occur, ascending
+    for label in np.unique(mask):
+        sl, (x, y, w, h) = so.slice_image(rgba, mask, int(label))
+        recs.append((int(label), "slice_%d.png" % label, x, y, w, h, sl))
+    assert (tmp_path / "wide" / "metadata.bin").read_bytes() == so.metadata_bytes(recs, W, H)
