@@ -391,6 +391,31 @@ int icr_estimate_png_size_segment(const uint8_t* img, int full_W, int full_H, in
     return ICR_OK;
 }
 
+static_assert(NOALLOC_MAX_ROWS == ICR_NOALLOC_MAX_ROWS, "the header's limit is the array's size");
+
+int icr_estimate_png_size_segment_noalloc(const uint8_t* img, int full_W, int full_H, int channels, const int64_t* labels,
+                                          const int32_t* counts_k, int64_t seg_id_k, int x0, int y0, int w, int h,
+                                          int32_t min_pixels, int L_min, float beta, float b_match_token, float gamma,
+                                          double overhead_base, int adaptive_filter, double* out_dev, uint32_t* dbg_row_costs,
+                                          uint8_t* dbg_filter_id, uint32_t* dbg_hist, unsigned long long* dbg_match,
+                                          icr_stream stream) {
+    if (!img || !labels || !counts_k || !out_dev) return fail(ICR_EINVAL, "null ptr");
+    if (channels < 1 || channels > 4) return fail(ICR_EINVAL, "channels must be 1..4");
+    cudaStream_t st = (cudaStream_t)stream;
+    if (w <= 0 || h <= 0) {
+        ICR_CUDA(cudaMemsetAsync(out_dev, 0, sizeof(double), st), "memset out");
+        return ICR_OK;
+    }
+    if (x0 < 0 || y0 < 0 || x0 + w > full_W || y0 + h > full_H) return fail(ICR_EINVAL, "bbox outside the image");
+    if (h > NOALLOC_MAX_ROWS)
+        return fail(ICR_ECAPACITY, "icr_estimate_png_size_segment_noalloc: bbox of " + std::to_string(h) + " rows, the static scratch holds " +
+                                       std::to_string(NOALLOC_MAX_ROWS) + " (ICR_NOALLOC_MAX_ROWS); use icr_estimate_png_size_segment");
+    icr_params prm{min_pixels, L_min, beta, b_match_token, gamma, overhead_base, adaptive_filter, 0.0};
+    ICR_CUDA(launch_single_segment_noalloc(img, full_W, full_H, channels, labels, seg_id_k, x0, y0, w, h, widen(&prm), out_dev,
+                                           dbg_row_costs, dbg_filter_id, dbg_hist, dbg_match, st), "single segment (static scratch)");
+    return ICR_OK;
+}
+
 int icr_workspace_tables(icr_workspace* ws, const int32_t** K, const int32_t** counts, const int32_t** bboxes,
                          const double** seg_sizes, const long long** keys, int* Kmax) {
     if (!ws) return fail(ICR_EINVAL, "workspace is null");

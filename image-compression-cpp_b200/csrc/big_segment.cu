@@ -9,6 +9,7 @@
 // bytes and feeds the histogram, then a thread per reference chunk walks its bytes for the run statistics.
 // Entropy and mean follow the reference's reduction trees (:281-328) exactly.
 #include "icr_internal.h"
+#include <mutex>
 #include "icr_pixel.cuh"
 #include "icr_reward.cuh"
 
@@ -462,6 +463,47 @@ cudaError_t launch_single_segment(const uint8_t* img, int W, int H, int channels
     SrcRaw src{img, labels, W, channels, k};
     BigDebug d{row_costs, filter_id, hist, match, nullptr};
     single_segment_kernel<<<1, BIG_T, 0, st>>>(src, x0, y0, w, h, p, filter_scratch, out, d);
+    count_launch();
+    return cudaGetLastError();
+}
+
+// ---- the same launch for callers that may not allocate (CUDA graph capture, serving loops): the h bytes of filter-id
+// scratch live in a file-scope device array that every GPU loading the library holds until exit.  All calls on a device
+// share it: block_segment writes filt[y] of every row before it reads it, so nothing has to be cleared between calls,
+// but two calls that overlap on the GPU (different streams) race on it.
+static __device__ __align__(256) uint8_t g_noalloc_filter[NOALLOC_MAX_ROWS];
+
+// device address of the array on the current device: in host code the symbol is only a handle, the address comes
+// from the runtime, once per device
+static cudaError_t noalloc_filter_ptr(uint8_t** out) {
+    static std::mutex mu;
+    static uint8_t* ptr[16] = {nullptr};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= 16) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(mu);
+    if (!ptr[dev]) {
+        uint8_t* q = nullptr;
+        e = cudaGetSymbolAddress((void**)&q, g_noalloc_filter);
+        if (e != cudaSuccess) return e;
+        ptr[dev] = q;
+    }
+    *out = ptr[dev];
+    return cudaSuccess;
+}
+
+cudaError_t launch_single_segment_noalloc(const uint8_t* img, int W, int H, int channels, const int64_t* labels, int64_t k,
+                                          int x0, int y0, int w, int h, const EstParams& p, double* out, uint32_t* row_costs,
+                                          uint8_t* filter_id, uint32_t* hist, unsigned long long* match, cudaStream_t st) {
+    (void)H;
+    if (h > NOALLOC_MAX_ROWS) return cudaErrorInvalidValue;
+    uint8_t* filt = nullptr;
+    cudaError_t e = noalloc_filter_ptr(&filt);
+    if (e != cudaSuccess) return e;
+    SrcRaw src{img, labels, W, channels, k};
+    BigDebug d{row_costs, filter_id, hist, match, nullptr};
+    single_segment_kernel<<<1, BIG_T, 0, st>>>(src, x0, y0, w, h, p, filt, out, d);
     count_launch();
     return cudaGetLastError();
 }

@@ -153,6 +153,13 @@ cudaError_t launch_single_segment(const uint8_t* img, int W, int H, int channels
                                   int64_t k, int x0, int y0, int w, int h, const EstParams& p,
                                   double* out, uint32_t* row_costs, uint8_t* filter_id, uint32_t* hist,
                                   unsigned long long* match, uint8_t* filter_scratch, cudaStream_t st);
+// same launch with the filter-id scratch in a file-scope __device__ array (big_segment.cu): no allocation of any kind.
+// h above NOALLOC_MAX_ROWS is the caller's error (checked in api.cu).
+constexpr int NOALLOC_MAX_ROWS = 16384;
+cudaError_t launch_single_segment_noalloc(const uint8_t* img, int W, int H, int channels, const int64_t* labels,
+                                          int64_t k, int x0, int y0, int w, int h, const EstParams& p,
+                                          double* out, uint32_t* row_costs, uint8_t* filter_id, uint32_t* hist,
+                                          unsigned long long* match, cudaStream_t st);
 cudaError_t launch_ema(const double* rewards, int n, const double* sum_count, double momentum,
                        double* state, double* adv, const unsigned long long* flags, int ranks, unsigned long long step,
                        cudaStream_t st);

@@ -136,6 +136,27 @@ int icr_estimate_png_size_segment(const uint8_t* img_hwc_u8, int full_W, int ful
                                   uint32_t* dbg_hist, unsigned long long* dbg_match,
                                   icr_stream stream);
 
+/* The same estimate for callers that may not allocate (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * Same arguments, same result as icr_estimate_png_size_segment; the h bytes
+ * of filter-id scratch that entry allocates (cudaMallocAsync, grow-only) live here in a static device
+ * array of ICR_NOALLOC_MAX_ROWS bytes that every GPU loading the library holds until exit.  Calls
+ * no cudaMalloc / cudaFree or any allocating routine; h > ICR_NOALLOC_MAX_ROWS returns ICR_ECAPACITY.
+ * The first call on a device resolves the array's address (cudaGetSymbolAddress): make one call
+ * before capturing.  All calls on a device share the array (nothing in it has to be cleared: every
+ * row's filter id is written before it is read), so calls that overlap on the GPU -- different
+ * streams, or graph branches -- race; order them on one stream. */
+#define ICR_NOALLOC_MAX_ROWS 16384
+int icr_estimate_png_size_segment_noalloc(const uint8_t* img_hwc_u8, int full_W, int full_H, int channels,
+                                          const int64_t* labels_compact_hw, const int32_t* counts_k,
+                                          int64_t seg_id_k, int x0, int y0, int w, int h,
+                                          int32_t min_pixels, int L_min, float beta, float b_match_token,
+                                          float gamma, double overhead_base, int adaptive_filter,
+                                          double* out_dev,
+                                          uint32_t* dbg_row_costs, uint8_t* dbg_filter_id,
+                                          uint32_t* dbg_hist, unsigned long long* dbg_match,
+                                          icr_stream stream);
+
 /* ---- read-back of the tables the last icr_compute_rewards / icr_segment_stats left in the
  * workspace (device pointers, valid until the next call): K int32 [V], counts int32 [V,Kmax],
  * bboxes int32 [V,Kmax,4], seg_sizes f64 [V,Kmax], keys i64 [V,Kmax] = original label of compact id k. */
