@@ -19,6 +19,8 @@ struct icr_workspace {
     // device staging for the host-buffer entry
     float* st_images; void* st_labels; double* st_sizes; double* st_rewards;
     size_t st_images_bytes, st_labels_bytes;
+    uint8_t* st_raw_images; uint16_t* st_raw_labels;      // u8 pixels / u16 labels as they came over the link (icr_compute_rewards_host_u8)
+    size_t st_raw_images_bytes, st_raw_labels_bytes;
     cudaStream_t copy_stream;      // the host-buffer entry copies the next chunk on it while the current one is computed
     cudaEvent_t copy_ev[HOST_CHUNKS + 1];
     int profile;           // record events between the kernels of icr_compute_rewards
@@ -34,6 +36,7 @@ static thread_local long long g_launches = 0;
 void count_launch(int n) { g_launches += n; }
 
 static int fail(int code, const std::string& msg) { g_err = msg; return code; }
+int api_fail(int code, const std::string& msg) { return fail(code, msg); }      // for the other translation units (exchange.cu)
 static int cuda_fail(cudaError_t e, const char* what) {
     return fail(ICR_ECUDA, std::string("CUDA error in ") + what + ": " + cudaGetErrorString(e));
 }
@@ -178,6 +181,7 @@ int icr_workspace_destroy(icr_workspace* ws) {
     cudaSetDevice(ws->device);
     cudaFree(ws->base);
     cudaFree(ws->st_images); cudaFree(ws->st_labels); cudaFree(ws->st_sizes); cudaFree(ws->st_rewards);
+    cudaFree(ws->st_raw_images); cudaFree(ws->st_raw_labels);
     if (ws->ev[0]) for (int i = 0; i < 5; ++i) cudaEventDestroy(ws->ev[i]);
     if (ws->copy_stream) {
         for (int i = 0; i <= HOST_CHUNKS; ++i) cudaEventDestroy(ws->copy_ev[i]);
@@ -240,26 +244,35 @@ int icr_compute_rewards_gather(const float* images, const void* labels, int labe
                                 rank * B * S, flags_of_rank_dev, step, rank, ws, stream);
 }
 
-int icr_compute_rewards_host(const float* images_h, const void* labels_h, int label_dtype, const double* image_sizes_h,
-                             int B, int S, int H, int W, const icr_params* params, double* rewards_h,
-                             icr_workspace* ws, icr_stream stream) {
+// The host-buffer entries.  image_kind: 0 f32 planar (the reference's tensor), 1 u8 planar, 2 u8 interleaved.
+static int grow(void** p, size_t* have, size_t want, const char* what) {
+    if (*have >= want) return ICR_OK;
+    cudaFree(*p); *p = nullptr; *have = 0;
+    ICR_CUDA(cudaMalloc(p, want), what);
+    *have = want;
+    return ICR_OK;
+}
+
+static int host_entry(const void* images_h, int image_kind, const void* labels_h, int label_dtype, const double* image_sizes_h,
+                      int B, int S, int H, int W, const icr_params* params, double* rewards_h, icr_workspace* ws, icr_stream stream) {
     if (!images_h || !labels_h || !image_sizes_h || !rewards_h || !params) return fail(ICR_EINVAL, "null ptr");
-    if (label_dtype != ICR_LABELS_I32 && label_dtype != ICR_LABELS_I64) return fail(ICR_EINVAL, "labels must be int32 or int64");
+    const bool u16 = label_dtype == ICR_LABELS_U16;
+    if (label_dtype != ICR_LABELS_I32 && label_dtype != ICR_LABELS_I64 && !(u16 && image_kind != 0))
+        return fail(ICR_EINVAL, image_kind ? "labels must be int32, int64 or uint16" : "labels must be int32 or int64");
     if (B <= 0 || S <= 0) return fail(ICR_EINVAL, "B and S must be positive");
     if (int rc = check_shape(ws, B * S, H, W)) return rc;
     cudaStream_t st = (cudaStream_t)stream;
     const size_t HW = (size_t)H * W;
-    const size_t ib = (size_t)B * 3 * HW * 4, lb = (size_t)B * S * HW * (label_dtype == ICR_LABELS_I64 ? 8 : 4);
-    if (ws->st_images_bytes < ib) {
-        cudaFree(ws->st_images); ws->st_images = nullptr; ws->st_images_bytes = 0;
-        ICR_CUDA(cudaMalloc((void**)&ws->st_images, ib), "cudaMalloc(staging images)");
-        ws->st_images_bytes = ib;
-    }
-    if (ws->st_labels_bytes < lb) {
-        cudaFree(ws->st_labels); ws->st_labels = nullptr; ws->st_labels_bytes = 0;
-        ICR_CUDA(cudaMalloc(&ws->st_labels, lb), "cudaMalloc(staging labels)");
-        ws->st_labels_bytes = lb;
-    }
+    const size_t isz = image_kind ? 1 : 4;                                    // bytes per image element on the host
+    const size_t lsz = label_dtype == ICR_LABELS_I64 ? 8 : (u16 ? 2 : 4);     // bytes per label on the host
+    const size_t dev_lsz = label_dtype == ICR_LABELS_I64 ? 8 : 4;             // and on the device
+    const int dev_dtype = u16 ? ICR_LABELS_I32 : label_dtype;
+    if (int rc = grow((void**)&ws->st_images, &ws->st_images_bytes, (size_t)B * 3 * HW * 4, "cudaMalloc(staging images)")) return rc;
+    if (int rc = grow(&ws->st_labels, &ws->st_labels_bytes, (size_t)B * S * HW * dev_lsz, "cudaMalloc(staging labels)")) return rc;
+    if (image_kind)
+        if (int rc = grow((void**)&ws->st_raw_images, &ws->st_raw_images_bytes, (size_t)B * 3 * HW, "cudaMalloc(staging u8 images)")) return rc;
+    if (u16)
+        if (int rc = grow((void**)&ws->st_raw_labels, &ws->st_raw_labels_bytes, (size_t)B * S * HW * 2, "cudaMalloc(staging u16 labels)")) return rc;
     if (!ws->st_sizes) {
         ICR_CUDA(cudaMalloc((void**)&ws->st_sizes, (size_t)ws->V * 8), "cudaMalloc(staging sizes)");
         ICR_CUDA(cudaMalloc((void**)&ws->st_rewards, (size_t)ws->V * 8), "cudaMalloc(staging rewards)");
@@ -272,7 +285,8 @@ int icr_compute_rewards_host(const float* images_h, const void* labels_h, int la
     // c, so the call costs the transfer plus the kernels of the last piece only.  The copies start after whatever the
     // caller's stream still has queued (an earlier call may be reading the staging buffers).
     const int nchunk = B >= 16 * HOST_CHUNKS ? HOST_CHUNKS : 1;
-    const size_t lsz = label_dtype == ICR_LABELS_I64 ? 8 : 4;
+    char* img_dst = image_kind ? (char*)ws->st_raw_images : (char*)ws->st_images;
+    char* lab_dst = u16 ? (char*)ws->st_raw_labels : (char*)ws->st_labels;
     ICR_CUDA(cudaEventRecord(ws->copy_ev[HOST_CHUNKS], st), "event record");
     ICR_CUDA(cudaStreamWaitEvent(ws->copy_stream, ws->copy_ev[HOST_CHUNKS], 0), "stream wait");
     ICR_CUDA(cudaMemcpyAsync(ws->st_sizes, image_sizes_h, (size_t)B * 8, cudaMemcpyHostToDevice, st), "H2D sizes");
@@ -280,20 +294,52 @@ int icr_compute_rewards_host(const float* images_h, const void* labels_h, int la
     for (int c = 0; c <= nchunk; ++c) b0[c] = (int)((long long)B * c / nchunk);
     for (int c = 0; c < nchunk; ++c) {
         const size_t io = (size_t)b0[c] * 3 * HW, lo = (size_t)b0[c] * S * HW, n = (size_t)(b0[c + 1] - b0[c]);
-        ICR_CUDA(cudaMemcpyAsync(ws->st_images + io, images_h + io, n * 3 * HW * 4, cudaMemcpyHostToDevice, ws->copy_stream), "H2D images");
-        ICR_CUDA(cudaMemcpyAsync((char*)ws->st_labels + lo * lsz, (const char*)labels_h + lo * lsz, n * S * HW * lsz, cudaMemcpyHostToDevice,
+        ICR_CUDA(cudaMemcpyAsync(img_dst + io * isz, (const char*)images_h + io * isz, n * 3 * HW * isz, cudaMemcpyHostToDevice,
+                                 ws->copy_stream), "H2D images");
+        ICR_CUDA(cudaMemcpyAsync(lab_dst + lo * lsz, (const char*)labels_h + lo * lsz, n * S * HW * lsz, cudaMemcpyHostToDevice,
                                  ws->copy_stream), "H2D labels");
         ICR_CUDA(cudaEventRecord(ws->copy_ev[c], ws->copy_stream), "event record");
     }
     for (int c = 0; c < nchunk; ++c) {
+        const size_t io = (size_t)b0[c] * 3 * HW, lo = (size_t)b0[c] * S * HW, n = (size_t)(b0[c + 1] - b0[c]);
         ICR_CUDA(cudaStreamWaitEvent(st, ws->copy_ev[c], 0), "stream wait");
-        if (int rc = icr_compute_rewards(ws->st_images + (size_t)b0[c] * 3 * HW, (const char*)ws->st_labels + (size_t)b0[c] * S * HW * lsz,
-                                         label_dtype, ws->st_sizes + b0[c], b0[c + 1] - b0[c], S, H, W, params,
-                                         ws->st_rewards + (size_t)b0[c] * S, ws, stream)) return rc;
+        if (image_kind || u16)
+            ICR_CUDA(launch_expand(image_kind ? ws->st_raw_images + io : nullptr, image_kind == 2, ws->st_images + io, (int64_t)n, (int64_t)HW,
+                                   u16 ? ws->st_raw_labels + lo : nullptr, (int32_t*)ws->st_labels + lo, (int64_t)(n * S * HW), st), "expand");
+        if (int rc = icr_compute_rewards(ws->st_images + io, (const char*)ws->st_labels + lo * dev_lsz, dev_dtype, ws->st_sizes + b0[c],
+                                         (int)n, S, H, W, params, ws->st_rewards + (size_t)b0[c] * S, ws, stream)) return rc;
     }
     if (nchunk > 1) ws->in = Inputs{nullptr, nullptr, 0, 1};      // the tables describe the last piece only: no debug/slice entry after this call
     ICR_CUDA(cudaMemcpyAsync(rewards_h, ws->st_rewards, (size_t)B * S * 8, cudaMemcpyDeviceToHost, st), "D2H rewards");
     ICR_CUDA(cudaStreamSynchronize(st), "stream sync");
+    return ICR_OK;
+}
+
+int icr_compute_rewards_host(const float* images_h, const void* labels_h, int label_dtype, const double* image_sizes_h,
+                             int B, int S, int H, int W, const icr_params* params, double* rewards_h,
+                             icr_workspace* ws, icr_stream stream) {
+    return host_entry(images_h, 0, labels_h, label_dtype, image_sizes_h, B, S, H, W, params, rewards_h, ws, stream);
+}
+
+int icr_compute_rewards_host_u8(const uint8_t* images_u8_h, int image_layout, const void* labels_h, int label_dtype,
+                                const double* image_sizes_h, int B, int S, int H, int W, const icr_params* params,
+                                double* rewards_h, icr_workspace* ws, icr_stream stream) {
+    if (image_layout != ICR_U8_PLANAR && image_layout != ICR_U8_INTERLEAVED) return fail(ICR_EINVAL, "image_layout must be ICR_U8_PLANAR or ICR_U8_INTERLEAVED");
+    return host_entry(images_u8_h, image_layout == ICR_U8_INTERLEAVED ? 2 : 1, labels_h, label_dtype, image_sizes_h, B, S, H, W, params,
+                      rewards_h, ws, stream);
+}
+
+int icr_pack_node_labels(const int32_t* const* node_mapping_dev_ptrs, const int64_t* node_mapping_sizes, int B, int64_t N,
+                         int32_t* labels_bn_out, icr_stream stream) {
+    if (!node_mapping_dev_ptrs || !labels_bn_out) return fail(ICR_EINVAL, "null ptr");
+    if (B <= 0 || N <= 0) return fail(ICR_EINVAL, "B and N must be positive");
+    for (int b = 0; b < B; ++b) {
+        if (!node_mapping_dev_ptrs[b]) return fail(ICR_EINVAL, "node_mapping " + std::to_string(b) + " is null");
+        if (node_mapping_sizes && node_mapping_sizes[b] != N)                                            // src/rama_wrapper.cu:116-117
+            return fail(ICR_EINVAL, "node_mapping " + std::to_string(b) + " has " + std::to_string(node_mapping_sizes[b]) +
+                                        " entries, expected N = " + std::to_string(N));
+    }
+    ICR_CUDA(launch_pack_labels(node_mapping_dev_ptrs, B, N, labels_bn_out, (cudaStream_t)stream), "pack labels");
     return ICR_OK;
 }
 

@@ -163,6 +163,10 @@ cudaError_t launch_single_segment_noalloc(const uint8_t* img, int W, int H, int 
 cudaError_t launch_ema(const double* rewards, int n, const double* sum_count, double momentum,
                        double* state, double* adv, const unsigned long long* flags, int ranks, unsigned long long step,
                        cudaStream_t st);
+cudaError_t launch_expand(const uint8_t* images_u8, int hwc, float* images_f32, int64_t B, int64_t HW, const uint16_t* labels_u16,
+                          int32_t* labels_i32, int64_t n_labels, cudaStream_t st);
+constexpr int PACK_MAX = 256;      // node_mapping pointers per launch of the label packer (kernel-parameter space)
+cudaError_t launch_pack_labels(const int32_t* const* ptrs_host, int B, int64_t N, int32_t* out, cudaStream_t st);
 cudaError_t launch_sum_count(const double* rewards, int n, double* sum_count, cudaStream_t st);
 cudaError_t run_selftest(int* mismatches);
 

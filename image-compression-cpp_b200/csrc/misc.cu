@@ -1,6 +1,7 @@
 // Small kernels around the estimator: slice materialisation of one segment (Rule P),
 // the compact-label stats drop-in (Rule S), EMA baseline + advantage (Rule E) and the self-test.
 #include "icr_internal.h"
+#include <algorithm>
 #include "icr_pixel.cuh"
 #include "icr_reward.cuh"
 
@@ -140,6 +141,98 @@ __global__ void __launch_bounds__(1024) ema_kernel(const double* r, int n, const
     const double value = s_value;
     const double adv_mean = local_mean - value;
     for (int i = threadIdx.x; i < n; i += blockDim.x) adv[i] = ((__ldcg(r + i) - value) - adv_mean) / sd;
+}
+
+// ---- what a data loader holds before its float conversion (include/fcn/EdgeDataset.h:73): u8 pixels, and label ids that
+// fit 16 bits whenever H*W <= 65536.  The host-buffer entry can take those over the link (5 instead of 16 bytes per pixel)
+// and widen them here into the f32 planes / int32 labels the path reads; (float)u8 is exact, so Rule C gives the byte back.
+__global__ void __launch_bounds__(256) expand_planar_kernel(const uint8_t* __restrict__ src, float* __restrict__ dst, int64_t n, int vec) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x, t0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (vec) {
+        const uchar4* s4 = reinterpret_cast<const uchar4*>(src);
+        float4* d4 = reinterpret_cast<float4*>(dst);
+        for (int64_t i = t0; i < (n >> 2); i += stride) {
+            const uchar4 u = __ldg(s4 + i);
+            d4[i] = make_float4((float)u.x, (float)u.y, (float)u.z, (float)u.w);
+        }
+    } else {
+        for (int64_t i = t0; i < n; i += stride) dst[i] = (float)__ldg(src + i);
+    }
+}
+
+// interleaved [B,H,W,3] -> planar [B,3,H,W]; a thread per pixel
+__global__ void __launch_bounds__(256) expand_hwc_kernel(const uint8_t* __restrict__ src, float* __restrict__ dst, int64_t B, int64_t HW) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < B * HW; i += stride) {
+        const int64_t b = i / HW, p = i - b * HW;
+        const uint8_t* q = src + 3 * i;
+        float* d = dst + b * 3 * HW + p;
+        d[0] = (float)__ldg(q); d[HW] = (float)__ldg(q + 1); d[2 * HW] = (float)__ldg(q + 2);
+    }
+}
+
+__global__ void __launch_bounds__(256) expand_u16_kernel(const uint16_t* __restrict__ src, int32_t* __restrict__ dst, int64_t n, int vec) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x, t0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (vec) {
+        const ushort4* s4 = reinterpret_cast<const ushort4*>(src);
+        int4* d4 = reinterpret_cast<int4*>(dst);
+        for (int64_t i = t0; i < (n >> 2); i += stride) {
+            const ushort4 u = __ldg(s4 + i);
+            d4[i] = make_int4(u.x, u.y, u.z, u.w);
+        }
+    } else {
+        for (int64_t i = t0; i < n; i += stride) dst[i] = (int32_t)__ldg(src + i);
+    }
+}
+
+cudaError_t launch_expand(const uint8_t* images_u8, int hwc, float* images_f32, int64_t B, int64_t HW, const uint16_t* labels_u16,
+                          int32_t* labels_i32, int64_t n_labels, cudaStream_t st) {
+    const int grid = sm_count() * 8;
+    if (images_u8) {
+        const int64_t n = B * 3 * HW;
+        if (hwc) expand_hwc_kernel<<<grid, 256, 0, st>>>(images_u8, images_f32, B, HW);
+        else expand_planar_kernel<<<grid, 256, 0, st>>>(images_u8, images_f32, n,
+                                                        (n & 3) == 0 && (reinterpret_cast<uintptr_t>(images_u8) & 3) == 0 &&
+                                                            (reinterpret_cast<uintptr_t>(images_f32) & 15) == 0);
+        count_launch();
+    }
+    if (labels_u16) {
+        expand_u16_kernel<<<grid, 256, 0, st>>>(labels_u16, labels_i32, n_labels,
+                                                (n_labels & 3) == 0 && (reinterpret_cast<uintptr_t>(labels_u16) & 7) == 0 &&
+                                                    (reinterpret_cast<uintptr_t>(labels_i32) & 15) == 0);
+        count_launch();
+    }
+    return cudaGetLastError();
+}
+
+// ---- the producer side of the label handoff (src/rama_wrapper.cu:102-124): the solver returns one node_mapping vector per
+// sample, which the reference copies into out[b] with one thrust::copy (a launch) per sample.  Here up to PACK_MAX vectors
+// travel as kernel parameters and one launch writes their rows of the [B,N] plane.
+struct PackPtrs { const int32_t* p[PACK_MAX]; };
+
+__global__ void __launch_bounds__(256) pack_labels_kernel(PackPtrs src, int64_t N, int32_t* __restrict__ out) {
+    const int32_t* s = src.p[blockIdx.y];
+    int32_t* d = out + (int64_t)blockIdx.y * N;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x, t0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (((reinterpret_cast<uintptr_t>(s) | reinterpret_cast<uintptr_t>(d)) & 15) == 0) {
+        const int64_t n4 = N >> 2;
+        for (int64_t i = t0; i < n4; i += stride) reinterpret_cast<int4*>(d)[i] = __ldg(reinterpret_cast<const int4*>(s) + i);
+        for (int64_t i = (n4 << 2) + t0; i < N; i += stride) d[i] = __ldg(s + i);
+    } else {
+        for (int64_t i = t0; i < N; i += stride) d[i] = __ldg(s + i);
+    }
+}
+
+cudaError_t launch_pack_labels(const int32_t* const* ptrs_host, int B, int64_t N, int32_t* out, cudaStream_t st) {
+    const int bx = (int)std::min<int64_t>((N + 4 * 256 - 1) / (4 * 256), 64);
+    for (int b0 = 0; b0 < B; b0 += PACK_MAX) {
+        const int nb = std::min(PACK_MAX, B - b0);
+        PackPtrs pp;
+        for (int i = 0; i < nb; ++i) pp.p[i] = ptrs_host[b0 + i];
+        pack_labels_kernel<<<dim3(bx, nb), 256, 0, st>>>(pp, N, out + (int64_t)b0 * N);
+        count_launch();
+    }
+    return cudaGetLastError();
 }
 
 cudaError_t launch_sum_count(const double* rewards, int n, double* sum_count, cudaStream_t st) {

@@ -18,6 +18,12 @@ struct EMABaseline {
     // then applies the identical update.
     torch::Tensor update_global(const torch::Tensor& rewards_local, const torch::Tensor& sum_count);
 
+    // Sharded batch, exchange included: all-gathers every rank's rewards (same count on every rank) and all-reduces
+    // {sum, count} with icr_exchange_rewards on the current stream -- `nccl_comm` is the caller's ncclComm_t -- then applies
+    // Rule E to the gathered vector, which is bit-identical to update() on the whole batch on one GPU.  `gathered_out`
+    // (optional) receives the rewards of all ranks in rank order.
+    torch::Tensor update_global(const torch::Tensor& rewards_local, void* nccl_comm, torch::Tensor* gathered_out = nullptr);
+
     // update() + the advantage of src/fcn/training.cpp:178-181: (r - value) standardised by the batch mean and the
     // population std clamped at 1e-6.  Returns {value, advantages like rewards}.
     std::pair<torch::Tensor, torch::Tensor> update_with_advantages(const torch::Tensor& rewards);

@@ -261,6 +261,29 @@ torch::Tensor labels_from_rama(const torch::Tensor& node_labels_bn_i32, int64_t 
     return node_labels_bn_i32.view({node_labels_bn_i32.size(0), H, W});
 }
 
+torch::Tensor labels_from_node_mappings(const std::vector<torch::Tensor>& node_mappings, int64_t H, int64_t W) {
+    TORCH_CHECK(!node_mappings.empty(), "no node_mapping given");
+    TORCH_CHECK(H > 0 && W > 0, "Invalid number of nodes");                                  // :96
+    const int64_t B = (int64_t)node_mappings.size(), N = H * W;
+    const auto dev = node_mappings[0].device();
+    std::vector<const int32_t*> ptrs(B);
+    std::vector<int64_t> sizes(B);
+    for (int64_t b = 0; b < B; ++b) {
+        const auto& m = node_mappings[b];
+        TORCH_CHECK(m.is_cuda() && m.device() == dev, "node_mappings must be on one CUDA device");
+        TORCH_CHECK(m.scalar_type() == torch::kInt32 && m.is_contiguous(), "node_mappings must be contiguous int32");
+        TORCH_CHECK(m.numel() == N, "rama_cuda returned node_mapping of unexpected size");    // :116-117
+        ptrs[b] = m.data_ptr<int32_t>();
+        sizes[b] = m.numel();
+    }
+    c10::cuda::CUDAGuard dg(dev);
+    auto out = torch::empty({B, H, W}, node_mappings[0].options());
+    const int rc = icr_pack_node_labels(ptrs.data(), sizes.data(), (int)B, N, out.data_ptr<int32_t>(), current_stream());
+    if (rc == ICR_ECUDA) throw_runtime();
+    TORCH_CHECK(rc == ICR_OK, icr_last_error());
+    return out;
+}
+
 // ------------------------------------------------------------------------------------------------ EMA baseline
 torch::Tensor EMABaseline::run(const torch::Tensor& rewards, const torch::Tensor* sum_count, torch::Tensor* adv) {
     torch::NoGradGuard ng;
@@ -301,6 +324,26 @@ torch::Tensor EMABaseline::update(const torch::Tensor& rewards) { return run(rew
 
 torch::Tensor EMABaseline::update_global(const torch::Tensor& rewards_local, const torch::Tensor& sum_count) {
     return run(rewards_local, &sum_count, nullptr);
+}
+
+torch::Tensor EMABaseline::update_global(const torch::Tensor& rewards_local, void* nccl_comm, torch::Tensor* gathered_out) {
+    torch::NoGradGuard ng;
+    TORCH_CHECK(rewards_local.is_cuda(), "rewards must be CUDA");
+    TORCH_CHECK(rewards_local.numel() > 0, "rewards must not be empty");
+    TORCH_CHECK(nccl_comm != nullptr, "nccl_comm is null");
+    c10::cuda::CUDAGuard dg(rewards_local.device());
+    torch::Tensor r = rewards_local.reshape({-1});
+    if (r.scalar_type() != torch::kFloat64) r = r.to(torch::kFloat64);
+    r = r.contiguous();
+    int ranks = 0;
+    TORCH_CHECK(icr_nccl_comm_ranks(nccl_comm, &ranks) == ICR_OK, icr_last_error());
+    auto gathered = torch::empty({(int64_t)ranks * r.numel()}, r.options());
+    auto sum_count = torch::empty({2}, r.options());
+    const int rc = icr_exchange_rewards(nccl_comm, r.data_ptr<double>(), (int)r.numel(), gathered.data_ptr<double>(),
+                                        sum_count.data_ptr<double>(), current_stream());
+    TORCH_CHECK(rc == ICR_OK, icr_last_error());
+    if (gathered_out) *gathered_out = gathered;
+    return run(gathered, nullptr, nullptr);      // the sum over the gathered vector in image order: the single-GPU value bit for bit
 }
 
 std::pair<torch::Tensor, torch::Tensor> EMABaseline::update_with_advantages(const torch::Tensor& rewards) {
@@ -411,6 +454,34 @@ int icrh_ema_two_steps(const double* r1_dev, const double* r2_dev, int n, int de
         const torch::Tensor v2 = b.update(torch::from_blob((void*)r2_dev, {n}, f64));
         values_out[0] = v1.item<double>();
         values_out[1] = v2.item<double>();
+    });
+}
+
+int icrh_ema_update_global_nccl(const double* rewards_local_dev, int n, int device, void* nccl_comm, int ranks, double* value_out,
+                                double* gathered_out_dev) {
+    return guarded([&] {
+        c10::cuda::CUDAGuard g(device);
+        auto opt = torch::TensorOptions().dtype(torch::kFloat64).device(torch::Device(torch::kCUDA, device));
+        auto r = torch::from_blob((void*)rewards_local_dev, {n}, opt);
+        EMABaseline ema;
+        torch::Tensor gathered;
+        auto v = ema.update_global(r, nccl_comm, &gathered);
+        TORCH_CHECK(gathered.numel() == (int64_t)ranks * n, "gathered has the wrong size");
+        torch::from_blob((void*)gathered_out_dev, {(int64_t)ranks * n}, opt).copy_(gathered);
+        *value_out = v.item<double>();
+    });
+}
+
+int icrh_labels_from_node_mappings(const int32_t* const* ptrs_dev, const int64_t* sizes, int B, int H, int W, int device, int32_t* out_dev) {
+    return guarded([&] {
+        c10::cuda::CUDAGuard g(device);
+        auto opt = torch::TensorOptions().dtype(torch::kInt32).device(torch::Device(torch::kCUDA, device));
+        std::vector<torch::Tensor> maps;
+        for (int b = 0; b < B; ++b) maps.push_back(torch::from_blob((void*)ptrs_dev[b], {sizes[b]}, opt));
+        auto out = labels_from_node_mappings(maps, H, W);
+        TORCH_CHECK(out.dim() == 3 && out.size(0) == B && out.size(1) == H && out.size(2) == W, "wrong shape");
+        torch::from_blob((void*)out_dev, {B, H, W}, opt).copy_(out);
+        torch::cuda::synchronize(device);
     });
 }
 

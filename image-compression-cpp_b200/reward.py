@@ -26,11 +26,11 @@ class IcrParams(C.Structure):
 
 
 SYMBOLS = ["icr_last_error", "icr_version", "icr_default_params", "icr_workspace_bytes", "icr_workspace_create",
-           "icr_workspace_destroy", "icr_compute_rewards", "icr_compute_rewards_gather", "icr_compute_rewards_host", "icr_check", "icr_check_detail",
+           "icr_workspace_destroy", "icr_compute_rewards", "icr_compute_rewards_gather", "icr_compute_rewards_host", "icr_compute_rewards_host_u8", "icr_check", "icr_check_detail",
            "icr_label_capacity", "icr_segment_stats", "icr_counts_bboxes_from_compact_labels",
            "icr_estimate_png_size_segment", "icr_estimate_png_size_segment_noalloc", "icr_workspace_tables", "icr_debug_segment", "icr_slice_segment",
            "icr_slices_prepare", "icr_slices_plan", "icr_slices_emit", "icr_reassemble_map", "icr_reassemble_batch", "icr_paste_slice", "icr_ema_update", "icr_ema_update_gathered", "icr_reward_sum_count", "icr_selftest", "icr_launch_count", "icr_workspace_set_profile",
-           "icr_profile_read"]
+           "icr_profile_read", "icr_pack_node_labels", "icr_nccl_unique_id", "icr_nccl_comm_create", "icr_nccl_comm_destroy", "icr_nccl_comm_ranks", "icr_exchange_rewards"]
 
 
 def lib():

@@ -62,8 +62,10 @@ class PipelinedGather:
     Per step: `buf = next_buffer()`, queue the kernels that fill `buf` on the current stream, `submit(consumer)`;
     `drain()` before reading results or closing a timed region."""
 
-    def __init__(self, n_local, device, group=None, dtype=torch.float64):
+    def __init__(self, n_local, device, group=None, dtype=torch.float64, gather=None):
         self.group = group
+        # gather(gathered, local) queues the exchange on the CURRENT stream; default: torch.distributed's all-gather
+        self.gather = gather or (lambda g, l: dist.all_gather_into_tensor(g, l, group=self.group))
         self.world = dist.get_world_size(group)
         self.side = torch.cuda.Stream(device=device)
         self.local = [torch.empty(n_local, dtype=dtype, device=device) for _ in range(2)]
@@ -83,7 +85,7 @@ class PipelinedGather:
         self.ready[par].record(torch.cuda.current_stream())
         with torch.cuda.stream(self.side):
             self.side.wait_event(self.ready[par])
-            dist.all_gather_into_tensor(self.gathered[par], self.local[par], group=self.group)
+            self.gather(self.gathered[par], self.local[par])
             consumer(self.gathered[par])
             self.done[par].record(self.side)
         self.n += 1
@@ -133,3 +135,51 @@ class PeerGather:
     def barrier(self):
         """Device-side barrier across ranks on the current stream (for callers that pass no flags)."""
         self.handle.barrier(channel=0)
+
+
+class NcclExchange:
+    """The exchange through the C ABI itself (icr_exchange_rewards: all-gather of the rewards + all-reduce of {sum, count}
+    in one NCCL group on the caller's stream), on a communicator of its own: rank 0 draws the id, torch.distributed (any
+    backend) carries its 128 bytes to the others.  With world == 1 no process group is needed."""
+
+    def __init__(self, device, group=None):
+        import ctypes as C
+        from . import reward
+        self.C, self.L = C, reward.lib()
+        self.device = torch.device(device)
+        init = dist.is_available() and dist.is_initialized()
+        self.world = dist.get_world_size(group) if init else 1
+        self.rank = dist.get_rank(group) if init else 0
+        ident = (C.c_ubyte * 128)()
+        if self.rank == 0:
+            self._check(self.L.icr_nccl_unique_id(ident))
+        if self.world > 1:
+            backend = dist.get_backend(group)
+            t = torch.tensor(list(ident), dtype=torch.uint8, device=self.device if backend == "nccl" else "cpu")
+            dist.broadcast(t, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+            ident = (C.c_ubyte * 128)(*t.cpu().tolist())
+        self.comm = C.c_void_p()
+        with torch.cuda.device(self.device):
+            self._check(self.L.icr_nccl_comm_create(C.byref(self.comm), ident, self.world, self.rank))
+        self.sum_count = torch.zeros(2, dtype=torch.float64, device=self.device)
+
+    def _check(self, rc):
+        if rc != 0:
+            raise RuntimeError(self.L.icr_last_error().decode())
+
+    def __call__(self, gathered, local):
+        """Queue the exchange on the current stream: gathered f64 [world*n] <- every rank's local f64 [n]; self.sum_count
+        receives the global {sum, count}."""
+        C = self.C
+        with torch.cuda.device(self.device):
+            self._check(self.L.icr_exchange_rewards(self.comm, C.c_void_p(local.data_ptr()), C.c_int(local.numel()),
+                                                    C.c_void_p(gathered.data_ptr()) if gathered is not None else None,
+                                                    C.c_void_p(self.sum_count.data_ptr()),
+                                                    C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+
+    def close(self):
+        if self.comm:
+            with torch.cuda.device(self.device):
+                torch.cuda.synchronize()
+                self.L.icr_nccl_comm_destroy(self.comm)
+            self.comm = self.C.c_void_p()

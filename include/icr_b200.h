@@ -28,6 +28,7 @@ extern "C" {
 
 #define ICR_LABELS_I32 0  /* what rama_torch_batched hands over: src/rama_wrapper.cu:99 */
 #define ICR_LABELS_I64 1  /* what compute_rewards_batched converts to: src/compute_rewards.cu:97 */
+#define ICR_LABELS_U16 2  /* host buffers of icr_compute_rewards_host_u8 only */
 
 typedef void* icr_stream;               /* a cudaStream_t */
 typedef struct icr_workspace icr_workspace;
@@ -95,6 +96,20 @@ int icr_compute_rewards_host(const float* images_h, const void* labels_h, int la
                              const double* image_sizes_h, int B, int S, int H, int W,
                              const icr_params* params, double* rewards_h,
                              icr_workspace* ws, icr_stream stream);
+
+/* The host-buffer entry for what a data loader holds BEFORE its float conversion
+ * (include/fcn/EdgeDataset.h:73 makes the f32 tensor from 8-bit pixels): u8 images, planar [B,3,H,W]
+ * (ICR_U8_PLANAR) or interleaved [B,H,W,3] in plane order (ICR_U8_INTERLEAVED), and labels as int32,
+ * int64 or -- ICR_LABELS_U16, this entry only -- uint16 ids (any map with H*W <= 65536 fits after
+ * ranking).  5 to 7 bytes per pixel cross the link instead of 16; a device kernel widens them into the
+ * f32 planes / int32 labels of icr_compute_rewards.  (float)u8 is exact and Rule C maps it back to the
+ * same byte, so the rewards equal those of icr_compute_rewards_host on the converted tensors bit for bit. */
+#define ICR_U8_PLANAR 0
+#define ICR_U8_INTERLEAVED 1
+int icr_compute_rewards_host_u8(const uint8_t* images_u8_h, int image_layout, const void* labels_h, int label_dtype,
+                                const double* image_sizes_h, int B, int S, int H, int W,
+                                const icr_params* params, double* rewards_h,
+                                icr_workspace* ws, icr_stream stream);
 
 /* Synchronises `stream` and reports data-dependent failures of the calls issued so far on this
  * workspace: returns ICR_EDATA (and the first offending label map in *first_bad, may be NULL)
@@ -220,6 +235,31 @@ int icr_reward_sum_count(const double* rewards, int n, double* sum_count, icr_st
 int icr_ema_update_gathered(const double* gathered, int n, const unsigned long long* flags_local, int ranks,
                             unsigned long long step, double momentum, double* state, double* advantages,
                             icr_stream stream);
+
+/* ---- producer side of the label handoff: the copy loop of rama_torch_batched (src/rama_wrapper.cu:102-124, one
+ * thrust::copy launch per sample from the solver's node_mapping vector into out[b]) as one launch per 256 samples.
+ * node_mapping_dev_ptrs: HOST array of B device pointers to int32 [N]; node_mapping_sizes (host, may be NULL): their
+ * lengths, each checked against N like the reference does (:116-117); labels_bn_out int32 [B,N] device, which
+ * icr_compute_rewards takes as [B,H,W] with N = H*W.  Asynchronous, no allocation. */
+int icr_pack_node_labels(const int32_t* const* node_mapping_dev_ptrs, const int64_t* node_mapping_sizes, int B, int64_t N,
+                         int32_t* labels_bn_out, icr_stream stream);
+
+/* ---- the exchange of a sharded batch (one process per GPU).  The reference is single-GPU:
+ * include/ema_baseline.hpp:13 takes the mean over the whole batch, which on N GPUs needs every rank's rewards.
+ * icr_exchange_rewards queues, on `stream` and inside one ncclGroupStart/End, an all-gather of the ranks' rewards
+ * (gathered f64 [ranks*n_local] device, in rank order = image order for contiguous shards; may be NULL) and an
+ * all-reduce of {sum, count} (sum_count f64 [2] device, out; may be NULL; this rank's part is computed here first).
+ * Every rank passes the same n_local.  Asynchronous, no allocation.  `comm` is an ncclComm_t of the NCCL the process
+ * already has loaded (libnccl.so.2 is bound with dlopen at the first call, ICR_NCCL_LIB overrides the path): the
+ * caller's own communicator, or one made by icr_nccl_comm_create from an id that rank 0 obtained with
+ * icr_nccl_unique_id and sent to the others by whatever means it has (128 bytes).  Create with the rank's device current. */
+typedef void* icr_nccl_comm;
+int icr_nccl_unique_id(unsigned char* id128);
+int icr_nccl_comm_create(icr_nccl_comm* comm, const unsigned char* id128, int ranks, int rank);
+int icr_nccl_comm_destroy(icr_nccl_comm comm);
+int icr_nccl_comm_ranks(icr_nccl_comm comm, int* ranks);
+int icr_exchange_rewards(icr_nccl_comm comm, const double* rewards_local, int n_local, double* gathered,
+                         double* sum_count, icr_stream stream);
 
 /* Exhaustive device self-test of the packed-byte filter arithmetic against scalar code
  * (all 2^24 Paeth triples, all Avg pairs, all cost bytes): *mismatches is a host int. Synchronous. */

@@ -302,6 +302,57 @@ def test_host_buffer_entry_matches_device_entry(icr, orc, dev, B, S):
             ws.slices()
 
 
+@pytest.mark.parametrize("B,S,layout,lab", [(5, 1, "planar", "u16"), (70, 1, "hwc", "u16"), (66, 2, "planar", "i32"), (9, 1, "hwc", "i64")])
+def test_host_u8_entry_matches_f32_entry(icr, orc, dev, B, S, layout, lab):
+    """icr_compute_rewards_host_u8: 8-bit pixels (planar or interleaved, what include/fcn/EdgeDataset.h:73 holds before its
+    float conversion) and 16-bit label ids over the link, widened on the device.  (float)u8 is exact and Rule C maps it back
+    to the byte, so the rewards must equal the f32 entry's on the converted tensors bit for bit; odd H*W exercises the
+    scalar widening path, the larger batches the four overlapped pieces."""
+    import ctypes as C
+    H, W = (45, 63) if B < 10 else (48, 64)
+    if S == 1:
+        images, labels, sizes = synth.make_batch(2, B=min(B, 8))
+        images, labels = images[:, :, :H, :W].copy(), labels[:, :H, :W].copy()
+    else:
+        images, labels, sizes = synth.make_multi_batch(B=8, S=S, H=H, W=W)
+    reps = -(-B // images.shape[0])
+    images = np.ascontiguousarray(np.tile(images, (reps, 1, 1, 1))[:B])
+    labels = np.ascontiguousarray(np.tile(labels, (reps,) + (1,) * (labels.ndim - 1))[:B])
+    sizes = np.ascontiguousarray(np.tile(sizes, reps)[:B])
+    u8 = np.clip(np.rint(images), 0, 255).astype(np.uint8)                     # the bytes Rule C makes of the synthetic planes
+    f32 = u8.astype(np.float32)
+    host_img = np.ascontiguousarray(u8.transpose(0, 2, 3, 1)) if layout == "hwc" else u8
+    if lab == "u16":
+        assert labels.min() >= 0 and labels.max() < 65536
+        host_lab, code = labels.astype(np.uint16), 2                              # ICR_LABELS_U16
+    elif lab == "i64":
+        host_lab, code = labels.astype(np.int64) - 7, 1
+    else:
+        host_lab, code = labels, 0
+    ws = icr.Workspace(dev, B * S, H, W, None)
+    out, want = np.zeros(B * S, np.float64), np.zeros(B * S, np.float64)
+    prm = icr.make_params()
+    L = icr.lib()
+    p = lambda a: a.ctypes.data_as(C.c_void_p)
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    with torch.cuda.device(dev):
+        for _ in range(2):                                                        # the second call reuses the staging buffers
+            out[:] = 0
+            rc = L.icr_compute_rewards_host_u8(p(host_img), int(layout == "hwc"), p(host_lab), code, p(sizes), B, S, H, W, C.byref(prm),
+                                               p(out), ws.handle, st)
+            assert rc == 0, L.icr_last_error()
+            ws.check()
+        rc = L.icr_compute_rewards_host(p(f32), p(labels), 0, p(sizes), B, S, H, W, C.byref(prm), p(want), ws.handle, st)
+        assert rc == 0, L.icr_last_error()
+        assert np.array_equal(out, want)
+        # u16 labels only through this entry, and only the two layouts
+        assert L.icr_compute_rewards_host(p(f32), p(labels), 2, p(sizes), B, S, H, W, C.byref(prm), p(want), ws.handle, st) != 0
+        assert L.icr_compute_rewards_host_u8(p(host_img), 5, p(host_lab), code, p(sizes), B, S, H, W, C.byref(prm), p(out), ws.handle, st) != 0
+    n = min(B, 8)
+    ref = orc.compute_rewards(np.repeat(f32[:n], S, axis=0), labels[:n].reshape(n * S, H, W), np.repeat(sizes[:n], S))
+    assert _rel(out[:n * S], ref) < RTOL
+
+
 @pytest.mark.parametrize("H,W", [(1, 1), (1, 17), (17, 1), (3, 4), (4, 4), (2, 8), (8, 16), (5, 1000), (300, 4), (33, 36)])
 def test_degenerate_shapes(icr, orc, dev, H, W):
     """One-pixel maps, single rows and columns, maps narrower than a quad and wider than a strip walk: every shape the

@@ -277,3 +277,34 @@ def test_cpp_slices_with_labels_beyond_the_bitmap_are_ranked(host, orc, dev, tmp
         sl, (x, y, w, h) = so.slice_image(rgba, mask, int(label))
         recs.append((int(label), "slice_%d.png" % label, x, y, w, h, sl))
     assert (tmp_path / "wide" / "metadata.bin").read_bytes() == so.metadata_bytes(recs, W, H)
+
+
+@pytest.mark.gpu
+def test_node_mapping_packer_c_abi_and_cpp(host, icr, dev):
+    """The producer side of the label handoff (src/rama_wrapper.cu:102-124): B per-sample node_mapping vectors -> one
+    [B,H,W] int32 plane.  300 samples cross the 256-pointer launch boundary; an odd N and a misaligned source take the
+    scalar path; a vector of the wrong length is refused with the reference's message."""
+    L = icr.lib()
+    rng = np.random.default_rng(12)
+    for B, H, W, shift in ((300, 16, 20, 0), (5, 15, 13, 0), (3, 16, 16, 1)):
+        N = H * W
+        backing = [torch.from_numpy(rng.integers(0, 1 << 30, N + 4, dtype=np.int32)).to(dev) for _ in range(B)]
+        maps = [t[shift:shift + N] for t in backing]
+        ptrs = (C.c_void_p * B)(*[m.data_ptr() for m in maps])
+        sizes = (C.c_int64 * B)(*[N] * B)
+        want = torch.stack(maps).view(B, H, W)
+        out = torch.zeros((B, H, W), dtype=torch.int32, device=dev)
+        with torch.cuda.device(dev):
+            rc = L.icr_pack_node_labels(ptrs, sizes, B, C.c_int64(N), _p(out), C.c_void_p(torch.cuda.current_stream().cuda_stream))
+        assert rc == 0, L.icr_last_error()
+        assert torch.equal(out, want)
+        out2 = torch.zeros_like(out)
+        rc = host.icrh_labels_from_node_mappings(ptrs, sizes, B, H, W, 0, _p(out2))
+        assert rc == 0, host.icrh_last_error()
+        assert torch.equal(out2, want)
+    sizes[1] = N - 1
+    with torch.cuda.device(dev):
+        assert L.icr_pack_node_labels(ptrs, sizes, B, C.c_int64(N), _p(out), None) != 0
+    assert "expected N" in L.icr_last_error().decode()
+    assert host.icrh_labels_from_node_mappings(ptrs, sizes, B, H, W, 0, _p(out2)) != 0
+    assert b"unexpected size" in host.icrh_last_error()
