@@ -155,6 +155,15 @@ def main():
     if "big" in which:          # adversarial for the warp path: every map is ONE whole-image segment (Rule M, chunk = 4), all through big_kernel
         im, lab, sz = synth.make_batch(2)
         run("big: 512 x 224x224, one whole-image segment per map", im, np.zeros_like(lab), sz, 8)
+    if "bg" in which:           # what multicut output looks like: compact segments on a background that touches all four borders
+        im, lab, sz = synth.make_batch(5, B=64)
+        lab = lab.copy()
+        for b in range(lab.shape[0]):
+            ids = np.unique(lab[b])
+            bg = np.random.default_rng(b).choice(ids, size=len(ids) // 3, replace=False)
+            lab[b][np.isin(lab[b], bg)] = -5
+            lab[b][0, :], lab[b][-1, :], lab[b][:, 0], lab[b][:, -1] = -5, -5, -5, -5
+        run("bg: 512 x 224x224, BSP rectangles on a border-touching background segment (a third of the rectangles)", im, lab, sz, 8)
     if "4" in which:
         im, lab, sz = synth.make_multi_batch(B=32, S=8)
         run("cfg4: 256 x 224x224, 8 label maps per image (rectangles / region growing)", im, lab, sz, 8)
