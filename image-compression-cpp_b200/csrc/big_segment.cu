@@ -104,6 +104,7 @@ __device__ void block_segment(const Src& src, int x0, int y0, int w, int h, int 
             for (int r = warp; r < nr; r += BIG_T / 32) {
                 uint32_t* dst = s_pix + r * w;
 #pragma unroll 4
+                ICR_DCHECK(r * w + w <= BIG_TILE_PX && w <= BAND_MAX_W && nr <= BAND_MAX_R);
                 for (int x = lane; x < w; x += 32) dst[x] = src.px(y0 + yb + r, x0 + x);
             }
             __syncthreads();

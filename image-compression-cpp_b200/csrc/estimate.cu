@@ -122,6 +122,7 @@ __device__ __forceinline__ void stage_rows(const float* __restrict__ img, const 
         for (int u = 0; u < U; ++u) {
             if (dst[u] >= 0) {
                 const uint32_t px = rgba_of(r[u], g[u], b[u]);
+                ICR_DCHECK(dst[u] < TILE_WORDS);
                 tile[dst[u]] = (FULL || l[u] == key) ? px : 0u;
             }
         }
@@ -172,7 +173,7 @@ __device__ __forceinline__ void stage_rows_vec(const float* __restrict__ img, co
                                         rgba_of(r[u].z, g[u].z, b[u].z), rgba_of(r[u].w, g[u].w, b[u].w)};
 #pragma unroll
                 for (int e = 0; e < 4; ++e)
-                    if ((unsigned)(xb[u] + e) < (unsigned)w) tile[dst[u] + e] = (FULL || l[u][e] == key) ? px[e] : 0u;
+                    if ((unsigned)(xb[u] + e) < (unsigned)w) { ICR_DCHECK(dst[u] + e >= 0 && dst[u] + e < TILE_WORDS); tile[dst[u] + e] = (FULL || l[u][e] == key) ? px[e] : 0u; }
             }
         }
     }
@@ -235,6 +236,7 @@ __device__ __forceinline__ void raw_convert(LT key, int w, int dx, int nq, float
             const int xb = 4 * (q - rr * nq) - dx;
             int slot = s0 + rr; if (slot > R) slot -= R + 1;
             const int dst = slot * tst + 1 + xb;
+            ICR_DCHECK(q < RW::quads && RW::parts * RW::quads <= RAW_BYTES / 16);
             const uint4 ur = raw[q], ug = raw[RW::quads + q], ub = raw[2 * RW::quads + q];
             LT l[4] = {key, key, key, key};
             if (!full) raw_labels(raw, RW::quads, q, l);
@@ -244,7 +246,7 @@ __device__ __forceinline__ void raw_convert(LT key, int w, int dx, int nq, float
                                     rgba_of(__uint_as_float(ur.w), __uint_as_float(ug.w), __uint_as_float(ub.w))};
 #pragma unroll
             for (int e = 0; e < 4; ++e)
-                if ((unsigned)(xb + e) < (unsigned)w) tile[dst + e] = l[e] == key ? px[e] : 0u;
+                if ((unsigned)(xb + e) < (unsigned)w) { ICR_DCHECK(dst + e >= 0 && dst + e < TILE_WORDS); tile[dst + e] = l[e] == key ? px[e] : 0u; }
         }
     }
 }
@@ -318,6 +320,9 @@ __device__ void warp_segment(const float* __restrict__ img, const LT* __restrict
         uint32_t* ppr = sm.ppae + sr * pst + xs;
 
         Costs5 c = {0, 0, 0, 0, 0};
+        ICR_DCHECK((R + 1) * tst <= TILE_WORDS && R * pst <= PLANE_WORDS && n <= MAXSW);
+        ICR_DCHECK(n == 0 || (trow - 1 >= tile && trow + n < tile + TILE_WORDS && urow - 1 >= tile && urow + n < tile + TILE_WORDS));
+        ICR_DCHECK(n == 0 || (par + n <= sm.pavg + PLANE_WORDS && ppr + n <= sm.ppae + PLANE_WORDS));
         if (n > 0) {
             uint32_t left = trow[-1], ul = urow[-1];
             uint32_t l_lo = unpack_lo(left), l_hi = unpack_hi(left), ul_lo = unpack_lo(ul), ul_hi = unpack_hi(ul);
@@ -378,6 +383,7 @@ __device__ void warp_segment(const float* __restrict__ img, const LT* __restrict
                 atomicAdd(hist + 256 + __byte_perm(r, 0, 0x4441), 1u);
                 atomicAdd(hist + 512 + __byte_perm(r, 0, 0x4442), 1u);
                 atomicAdd(hist + 768 + (r >> 24), 1u);
+                ICR_DCHECK(pred >= tile - 1 && (pred < tile + TILE_WORDS || (pred >= sm.pavg && pred <= sm.ppae + PLANE_WORDS)));
                 cur = ncur; pr = npr;
             }
         }

@@ -4,6 +4,16 @@
 #include <stdint.h>
 #include "../../include/icr_b200.h"
 
+// Bounds checks of our own (compute-sanitizer is not available on the GPU pool): a build with -DICR_CHECKED asserts every
+// index into the shared-memory tables and the workspace lists (tools/build_variants.sh all:checked:-DICR_CHECKED, then
+// ICR_LIB=tools/_variants/libicr_checked.so python -m pytest tests -m gpu).  A failed check aborts the kernel with file:line.
+#ifdef ICR_CHECKED
+#include <cassert>
+#define ICR_DCHECK(c) assert(c)
+#else
+#define ICR_DCHECK(c) ((void)0)
+#endif
+
 namespace icr {
 
 // status bits per label map

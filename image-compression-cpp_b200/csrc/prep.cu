@@ -69,6 +69,7 @@ struct StatsPtr { int32_t *cnt, *bx0, *by0, *bx1, *by1; int bst; };
 template <bool SMEM>
 __device__ __forceinline__ void add_run(const StatsPtr& st, int kc, int n, int xa, int y) {
     const int k = kc * st.bst;
+    ICR_DCHECK(kc >= 0 && xa >= 0 && y >= 0 && n > 0);
     atomicAdd(st.cnt + kc, n);
     if (SMEM) {
         atomicMin(st.bx0 + k, xa); atomicMax(st.bx1 + k, xa + n - 1);
@@ -96,6 +97,7 @@ __device__ __forceinline__ void append_segment(const Tables& t, bool have, int c
         base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
         if (have && cat == c) {
             const int64_t pos = base + __popc(m & ltm);
+            ICR_DCHECK(pos >= 0 && pos < t.list_cap);
             const uint2 e = make_uint2((uint32_t)v, (uint32_t)k);
             if (c == 0) t.list_a[pos] = e;
             else if (c == 1) t.list_b[pos] = e;
@@ -206,7 +208,7 @@ __global__ void __launch_bounds__(PREP_T, 4) prep_kernel(const LT* __restrict__ 
         if (listed)
             for (uint32_t w = w0; w < w1; ++w) {
                 uint32_t bits = chgw[w];
-                while (bits) { const int b = __ffs(bits) - 1; bits &= bits - 1; heads[hb++] = w * 32u + b; }
+                while (bits) { const int b = __ffs(bits) - 1; bits &= bits - 1; ICR_DCHECK(hb < (uint32_t)t.head_cap); heads[hb++] = w * 32u + b; }
             }
         __syncthreads();
 
@@ -215,6 +217,7 @@ __global__ void __launch_bounds__(PREP_T, 4) prep_kernel(const LT* __restrict__ 
         auto mark = [&](LT l) -> uint32_t {
             lo = min(lo, l); hi = max(hi, l);
             const uint32_t idx = (uint32_t)l & cmask, bit = 1u << (idx & 31);
+            ICR_DCHECK((idx >> 5) < (uint32_t)cap_words);
             if (!(bitmap[idx >> 5] & bit)) atomicOr(&bitmap[idx >> 5], bit);
             return idx;
         };
@@ -291,6 +294,7 @@ __global__ void __launch_bounds__(PREP_T, 4) prep_kernel(const LT* __restrict__ 
                     const int b = __ffs(bits) - 1;
                     bits &= bits - 1;
                     const uint32_t slot = (uint32_t)w * 32u + b;
+                    ICR_DCHECK(rank_slot(slot) < (uint32_t)K && K <= t.Kmax);
                     keys[rank_slot(slot)] = lmin + (long long)((slot - smin) & cmask);
                 }
             }
