@@ -556,6 +556,34 @@ def main():
     }
     if e2e_cpp:
         line["e2e_cpp"] = e2e_cpp
+    if world == 1 and args.config == 5:
+        # Next to the headline, whose rectangles all fill their bboxes (the estimator then never reads a label): the same
+        # batch with a third of each map's rectangles melted into a background that touches all four borders, which is what
+        # multicut output looks like -- masked segments on the warp path, one whole-image Rule M segment per map on the
+        # big-segment kernel.
+        lab2 = wl.labels[:wl.pool].copy()
+        for b in range(lab2.shape[0]):
+            ids = np.unique(lab2[b])
+            bg = np.random.default_rng(b).choice(ids, size=len(ids) // 3, replace=False)
+            lab2[b][np.isin(lab2[b], bg)] = -5
+            lab2[b][0, :], lab2[b][-1, :], lab2[b][:, 0], lab2[b][:, -1] = -5, -5, -5, -5
+        reps = -(-B // wl.pool)
+        tl2 = torch.from_numpy(np.ascontiguousarray(np.tile(lab2, (reps, 1, 1))[:B])).to(dev)
+        r2 = torch.empty(V, dtype=torch.float64, device=dev)
+
+        def step_bg():
+            rc = L.icr_compute_rewards(p_i, C.c_void_p(tl2.data_ptr()), 0, p_s, B, S, H, W, C.byref(prm), C.c_void_p(r2.data_ptr()), ws.handle, stream)
+            if rc:
+                raise RuntimeError(L.icr_last_error().decode())
+        for _ in range(3):
+            step_bg()
+        ws.check()
+        bg_steps = max(3, min(args.steps, 10))
+        bg_ms = timed(step_bg, bg_steps) / bg_steps
+        line["irregular"] = {"workload": "the same batch with a third of each map's rectangles melted into a border-touching background segment",
+                             "value": B / (bg_ms * 1e-3), "unit": "images/sec", "ms_per_step": bg_ms,
+                             "mean_segments_per_label_map": float(np.mean([len(np.unique(m)) for m in lab2[:16]]))}
+        del tl2, r2
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cb, enc = cpu_baseline(wl)
         # per label map, the encoder's bytes next to the estimator's sum of S_k (a model of PNG size,

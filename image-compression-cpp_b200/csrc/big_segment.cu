@@ -35,6 +35,34 @@ struct SrcPlanar {          // the batch layout: the caller's f32 planes + raw l
         const float fr = __ldg(r + i), fg = __ldg(g + i), fb = __ldg(b + i);
         return l == key ? rgba_of(fr, fg, fb) : 0u;                                                  // Rule C, Rule P
     }
+    // rows widened to 16-byte boundaries can be fetched as float4 / int4 quads: W % 4 == 0 and aligned planes
+    __device__ __forceinline__ bool quads_ok() const {
+        return (W & 3) == 0 && (((uintptr_t)r | (uintptr_t)g | (uintptr_t)b | (uintptr_t)lab) & 15) == 0;
+    }
+    // masked pixels x0 .. x0+w-1 of row gy -> dst[0..w): a lane takes aligned quads, four pixels per load
+    __device__ __forceinline__ void row_quads(int gy, int x0, int w, uint32_t* dst, int lane) const {
+        const int x0a = x0 & ~3, dx = x0 - x0a, nq = (dx + w + 3) >> 2;
+        const uint32_t base = (uint32_t)gy * (uint32_t)W + (uint32_t)x0a;
+#pragma unroll 2
+        for (int q = lane; q < nq; q += 32) {
+            const uint32_t i = base + 4u * (uint32_t)q;
+            const float4 fr = __ldg(reinterpret_cast<const float4*>(r + i)), fg = __ldg(reinterpret_cast<const float4*>(g + i)),
+                         fb = __ldg(reinterpret_cast<const float4*>(b + i));
+            LT l[4];
+            if constexpr (sizeof(LT) == 4) {
+                const int4 v = __ldg(reinterpret_cast<const int4*>(lab + i));
+                l[0] = v.x; l[1] = v.y; l[2] = v.z; l[3] = v.w;
+            } else {
+                const longlong2 u = __ldg(reinterpret_cast<const longlong2*>(lab + i)), v = __ldg(reinterpret_cast<const longlong2*>(lab + i + 2));
+                l[0] = u.x; l[1] = u.y; l[2] = v.x; l[3] = v.y;
+            }
+            const uint32_t px4[4] = {rgba_of(fr.x, fg.x, fb.x), rgba_of(fr.y, fg.y, fb.y), rgba_of(fr.z, fg.z, fb.z), rgba_of(fr.w, fg.w, fb.w)};
+            const int xb = 4 * q - dx;
+#pragma unroll
+            for (int e = 0; e < 4; ++e)
+                if ((unsigned)(xb + e) < (unsigned)w) dst[xb + e] = l[e] == key ? px4[e] : 0u;
+        }
+    }
 };
 
 struct SrcRaw {             // the reference's layout: u8 [H,W,C] + compact int64 labels
@@ -46,6 +74,8 @@ struct SrcRaw {             // the reference's layout: u8 [H,W,C] + compact int6
         for (int c = 0; c < C; ++c) v |= (uint32_t)img[i * C + c] << (8 * c);
         return l == k ? v : 0u;
     }
+    __device__ __forceinline__ bool quads_ok() const { return false; }
+    __device__ __forceinline__ void row_quads(int, int, int, uint32_t*, int) const {}
 };
 
 __device__ __forceinline__ double size_formula_big(double Hbar, unsigned long long ms, unsigned long long mc,
@@ -87,13 +117,35 @@ __device__ void block_segment(const Src& src, int x0, int y0, int w, int h, int 
         while (b) { const int t = a % b; a = b; b = t; }       // gcd(w, wpc)
         const int g = wpc / a;                                 // rows per band must be a multiple of g
         R = min(min(h, BIG_TILE_PX / w), BAND_MAX_R);
-        if (R < h) R = (R / g) * g;                            // the last band may end anywhere: it ends the stream
+        if (R < h) {                                           // the last band may end anywhere: it ends the stream
+            R = (R / g) * g;
+            // the row phases give a row to a warp: a band whose rows are a multiple of the CTA's warps keeps all of them busy
+            // (224-wide bbox: 16 rows in two full rounds instead of 18 in three)
+            int a2 = g, b2 = BIG_T / 32;
+            while (b2) { const int t = a2 % b2; a2 = b2; b2 = t; }
+            const int l = g / a2 * (BIG_T / 32);               // lcm(g, warps)
+            if (R >= l) R = (R / l) * l;
+        }
     }
     if (R > 0) {
         __shared__ uint32_t s_pix[BIG_TILE_PX];
         __shared__ uint32_t s_halo[BAND_MAX_W];
         __shared__ uint8_t s_filt[BAND_MAX_R];
         const uint32_t wpc = (uint32_t)(chunk >> 2);
+        const bool quads = src.quads_ok();
+        // Rule M for chunks of ONE pixel (every bbox of 49 153 .. 65 536 pixels, e.g. a 224x224 image): a chunk's runs follow from
+        // which of its three byte pairs are equal, so {matched bytes, runs} of the eight cases sit in a table (low / high half
+        // of a word) and the residual walk adds its pixel's entry on the spot: no second pass, no residual tile
+        __shared__ uint32_t s_runs[8];
+        if (tid < 8) {
+            int run = 1, m = 0, n = 0;
+            for (int c = 0; c < 3; ++c) {
+                if (tid >> c & 1) ++run;
+                else { if (run >= p.L_min) { m += run; ++n; } run = 1; }
+            }
+            if (run >= p.L_min) { m += run; ++n; }
+            s_runs[tid] = (uint32_t)m | (uint32_t)n << 16;
+        }
         for (int yb = 0; yb < h; yb += R) {
             const int nr = min(R, h - yb);
             const int here = nr * w;
@@ -103,9 +155,12 @@ __device__ void block_segment(const Src& src, int x0, int y0, int w, int h, int 
             // a warp per row, lanes along x (these bboxes are wide: no row/column split per pixel)
             for (int r = warp; r < nr; r += BIG_T / 32) {
                 uint32_t* dst = s_pix + r * w;
-#pragma unroll 4
                 ICR_DCHECK(r * w + w <= BIG_TILE_PX && w <= BAND_MAX_W && nr <= BAND_MAX_R);
-                for (int x = lane; x < w; x += 32) dst[x] = src.px(y0 + yb + r, x0 + x);
+                if (quads) src.row_quads(y0 + yb + r, x0, w, dst, lane);
+                else {
+#pragma unroll 4
+                    for (int x = lane; x < w; x += 32) dst[x] = src.px(y0 + yb + r, x0 + x);
+                }
             }
             __syncthreads();
             // filter per row (Rule F): a warp per row, left neighbours by shuffle, lane 31's pixels carried to the next step
@@ -147,35 +202,25 @@ __device__ void block_segment(const Src& src, int x0, int y0, int w, int h, int 
                 const uint32_t* ur = r ? cr - w : s_halo;
                 uint32_t* rr = s_tile + r * w;
                 const int f = s_filt[r];
+                uint32_t acc = 0;                              // one-pixel chunks: matched bytes | runs << 16 of this lane's pixels (at most 4 and 2 each)
                 for (int x = lane; x < w; x += 32) {
                     const uint32_t cur = cr[x], up = ur[x];
                     const uint32_t left = x ? cr[x - 1] : 0u, ul = x ? ur[x - 1] : 0u;
                     const uint32_t r4 = residual4(f, cur, left, up, ul);
-                    rr[x] = r4;
+                    if (wpc == 1) {
+                        const uint32_t eq = r4 ^ (r4 >> 8);    // byte c is zero when residual bytes c and c+1 are equal
+                        acc += s_runs[((eq & 0xffu) ? 0u : 1u) | ((eq & 0xff00u) ? 0u : 2u) | ((eq & 0xff0000u) ? 0u : 4u)];
+                    } else rr[x] = r4;
                     atomicAdd(&s_hist[r4 & 255u], 1u);
                     atomicAdd(&s_hist[256 + ((r4 >> 8) & 255u)], 1u);
                     atomicAdd(&s_hist[512 + ((r4 >> 16) & 255u)], 1u);
                     atomicAdd(&s_hist[768 + (r4 >> 24)], 1u);
                 }
+                ms += acc & 0xffffu; mc += acc >> 16;
             }
             __syncthreads();
-            // run statistics (Rule M): a thread per reference chunk of wpc whole pixels.  A chunk of one pixel (every bbox up
-            // to 65536 pixels) is four bytes: its runs follow from the three neighbour comparisons without a loop.
-            if (wpc == 1) {
-                const int Lm = p.L_min;
-                for (int q = tid; q < here; q += BIG_T) {
-                    const uint32_t r4 = s_tile[q];
-                    const uint32_t eq = (r4 ^ (r4 >> 8));                  // byte c of eq is zero when bytes c and c+1 are equal
-                    const bool e1 = (eq & 0xffu) == 0, e2 = (eq & 0xff00u) == 0, e3 = (eq & 0xff0000u) == 0;
-                    // run lengths of the 4-byte string, left to right
-                    int run = 1, m = 0, n = 0;
-                    if (e1) ++run; else { if (run >= Lm) { m += run; ++n; } run = 1; }
-                    if (e2) ++run; else { if (run >= Lm) { m += run; ++n; } run = 1; }
-                    if (e3) ++run; else { if (run >= Lm) { m += run; ++n; } run = 1; }
-                    if (run >= Lm) { m += run; ++n; }
-                    ms += (unsigned long long)m; mc += (unsigned long long)n;
-                }
-            } else
+            if (wpc == 1) continue;                            // statistics already taken in the residual walk
+            // run statistics (Rule M): a thread per reference chunk of wpc whole pixels
             for (uint32_t w0 = (uint32_t)tid * wpc; w0 < (uint32_t)here; w0 += BIG_T * wpc) {
                 const uint32_t w1 = min(w0 + wpc, (uint32_t)here);
                 int prev = -1, run = 0;
