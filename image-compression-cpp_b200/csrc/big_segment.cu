@@ -163,22 +163,20 @@ __device__ void block_segment(const Src& src, int x0, int y0, int w, int h, int 
                 }
             }
             __syncthreads();
-            // filter per row (Rule F): a warp per row, left neighbours by shuffle, lane 31's pixels carried to the next step
+            // filter per row (Rule F): a warp per row
             for (int r = warp; r < nr; r += BIG_T / 32) {
                 int f = 4;
                 if (p.adaptive) {
                     Costs5 c = {0, 0, 0, 0, 0};
                     const uint32_t* cr = s_pix + r * w;
                     const uint32_t* ur = r ? cr - w : s_halo;
-                    uint32_t last_cur = 0u, last_up = 0u;
-                    for (int xb = 0; xb < w; xb += 32) {
-                        const int x = xb + lane;
-                        const uint32_t cur = x < w ? cr[x] : 0u, up = x < w ? ur[x] : 0u;
-                        uint32_t left = __shfl_up_sync(0xffffffffu, cur, 1), ul = __shfl_up_sync(0xffffffffu, up, 1);
-                        if (lane == 0) { left = last_cur; ul = last_up; }
-                        last_cur = __shfl_sync(0xffffffffu, cur, 31);
-                        last_up = __shfl_sync(0xffffffffu, up, 31);
-                        if (x < w) add_costs(c, cur, left, up, ul);
+                    // the band lies in shared memory: the left neighbours are two more loads, cheaper than four shuffles and
+                    // the fix-up of lane 0
+#pragma unroll 2
+                    for (int x = lane; x < w; x += 32) {
+                        const uint32_t cur = cr[x], up = ur[x];
+                        const uint32_t left = x ? cr[x - 1] : 0u, ul = x ? ur[x - 1] : 0u;
+                        add_costs(c, cur, left, up, ul);
                     }
                     for (int o = 16; o; o >>= 1) {
                         c.none += __shfl_xor_sync(0xffffffffu, c.none, o);
