@@ -3,7 +3,7 @@
 // Replaces the reference's 13 stream operations per segment (src/png_size_estimator.cu:505-590),
 // its two nested host loops (src/compute_rewards.cu:125,159) and its RGBA staging kernel (:23-53).
 //
-// Persistent warps pull segments from the work lists prep built (widest bboxes first), one per request with the next
+// Persistent warps pull segments from the work list prep built (in map order for this kernel), one per request with the next
 // request in flight.  A warp owns one segment and walks its bbox in groups of R rows:
 //   stage    every lane takes pixels of the group as aligned quads in row-major order (coalesced, all lanes busy
 //            whatever the width).  The quads of group g+1 are requested with cp.async into the warp's raw window
@@ -18,8 +18,8 @@
 //   residual second walk: predictor = one shared-memory load whose base/step depend on the row's filter
 //            (zero word, left, up, Avg plane, Paeth plane), the four residual bytes of every pixel of the bbox
 //            (zeros included) go to the warp's 4x256 histogram with unconditional ATOMS.POPC.INC.
-//   entropy  branch-free c*log2(c) table look-ups, Rule Z, one f64 store per segment; the warp that stores the last
-//            size of a label map also computes its reward (Rule W).
+//   entropy  branch-free c*log2(c) table look-ups, Rule Z, one f64 store per segment (Rule W waits for the tail kernel,
+//            big_segment.cu: signalling every segment cost more than its warp-per-map pass).
 // No residual stream, RGBA plane or compact-id plane is ever written to global memory.  Segments that
 // need Rule M match statistics (chunk >= L_min) or are wider than NARROW_MAX_W go to the big-segment kernel.
 // narrow.cu holds the other estimator for the same work lists (rows in registers, no tile); api.cu picks one.
@@ -443,7 +443,8 @@ __global__ void __launch_bounds__(EST_WARPS * 32, 4) estimate_kernel(Tables t, I
     for (int i = lane; i < 1024; i += 32) sm.hist[i] = 0;
     __syncwarp();
     const int64_t HW = (int64_t)t.H * t.W;
-    // the four work lists back to back, widest bboxes first: list_a front, list_b front, list_b back, list_a back
+    // the four work lists back to back (prep fills only the first for this kernel; by width class for narrow.cu):
+    // list_a front, list_b front, list_b back, list_a back
     const int e0 = t.sched[SC_N_W128], e1 = e0 + t.sched[SC_N_W64], e2 = e1 + t.sched[SC_N_W32], total = e2 + t.sched[SC_N_W16];
     const LT* labels = static_cast<const LT*>(in.labels);
     DebugOut none{};

@@ -17,8 +17,7 @@
 // atomic is predicated.
 // Wider bboxes (65..NARROW_MAX_W) take the same arithmetic chunk by chunk with the rows held in three small
 // shared-memory row buffers instead of registers (wide_rows): any width, one code path, few registers.
-// Epilogue: c*log2(c) table entropy, Rule Z, one f64 store; the warp that stores the last size of a label map also
-// computes its reward (Rule W).  Match statistics are zero here by construction: Rule M segments and bboxes wider than
+// Epilogue: c*log2(c) table entropy, Rule Z, one f64 store (Rule W is the tail kernel's, big_segment.cu).  Match statistics are zero here by construction: Rule M segments and bboxes wider than
 // NARROW_MAX_W go to the big-segment kernel.
 #include "icr_internal.h"
 #include "icr_pixel.cuh"

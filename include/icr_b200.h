@@ -267,8 +267,9 @@ int icr_selftest(int* mismatches);
 
 /* Measurement hook: with profiling on, icr_compute_rewards records CUDA events on `stream` between its
  * kernels; icr_profile_read waits for the last call and returns the device time in ms of its three launches
- * {prep (Rules L, S + work lists), narrow (register path: bboxes up to 128 wide without match statistics),
- *  big_segment (Rule M and wider segments + end-of-call bookkeeping), 0 (reserved)}. */
+ * {prep (Rules L, S + work lists), the estimator that ran (estimate_kernel, or narrow_kernel with ICR_ESTIMATOR=reg:
+ *  bboxes up to 224 wide without match statistics), big_kernel (Rule M and wider segments, Rule W of every map,
+ *  end-of-call bookkeeping), 0 (reserved)}. */
 int icr_workspace_set_profile(icr_workspace* ws, int on);
 int icr_profile_read(icr_workspace* ws, float* ms4);
 
