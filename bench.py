@@ -1,14 +1,15 @@
 #!/usr/bin/env python
 """bench.py -- images/sec through the compression-reward path (BASELINE.json metric).
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--config 5|3|4] [--scaling strong|weak]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--config 5|2|3|4] [--scaling strong|weak]
 
 A step is one pass of the path over one batch of synthetic input.  The default workload is BASELINE config 5 as written:
 4096 images of 224x224 RGB (f32 planes, bytes 0..255) with BSP-rectangle label maps (about 70 segments each, labels
 7*id+3), sharded over the N GPUs (strong scaling: 4096/N images per GPU; N=1 holds all 4096, 3.3 GB).  --scaling weak
 keeps 512 images per GPU instead (last round's line).  --config 3 (256 x 512x512, Voronoi maps of 1024 segments) and
---config 4 (256 x 224x224 with 8 label maps per image) print the same line for the other BASELINE configs.
-Inputs of one step exceed the 126 MB L2 in every case, so no flush is needed between iterations.
+--config 4 (256 x 224x224 with 8 label maps per image) and --config 2 (64 x 224x224, the batch of one training step; it
+fits the L2, so every step is timed on its own with the L2 flushed before it) print the same line for the other configs.
+Inputs of one step exceed the 126 MB L2 for configs 5, 3 and 4, so no flush is needed between their iterations.
 `value` is timed with CUDA events on the launching stream with inputs resident in HBM; `e2e` is the same metric through
 the C ABI's host-buffer entry (icr_compute_rewards_host: pinned host buffers, H2D and D2H inside the timed region).
 """
@@ -31,6 +32,8 @@ METRIC = "images/sec (slice+PNG-size reward)"
 # BASELINE.json configs: global batch, label maps per image, shape, table rows, distinct synthetic images per rank (the
 # batch tiles them: addresses differ, so nothing is reused from cache)
 CONFIGS = {
+    2: dict(G=64, S=1, H=224, W=224, Kmax=1024, pool=64,
+            name="cfg2: 64 x 224x224 RGB f32 planes, BSP-rectangle int32 label maps (~72 segments)"),
     5: dict(G=4096, S=1, H=224, W=224, Kmax=1024, pool=64,
             name="cfg5: 4096 x 224x224 RGB f32 planes, BSP-rectangle int32 label maps (labels 7*id+3)"),
     3: dict(G=256, S=1, H=512, W=512, Kmax=1024, pool=32,
@@ -56,7 +59,9 @@ class Workload:
         self.global_batch = self.B * world
         pool = min(c["pool"], self.B)
         first = rank * self.B                                       # index of this rank's first image in the global batch
-        if cfg == 5:
+        if cfg == 2:
+            images, labels, sizes = synth.make_batch(2, B=pool, seed0=1000 + first)
+        elif cfg == 5:
             images, labels, sizes = synth.make_batch(5, B=pool, seed0=5000 + first)
         elif cfg == 3:
             images, labels, sizes = synth.make_batch(3, B=pool, seed0=3000 + first)
@@ -220,7 +225,7 @@ def run_reference(args):
         return
     import torch
     wl = Workload(args.config, 0, 1, "strong")
-    n = min(wl.B, {5: 512, 3: 16, 4: 32}[args.config])           # images per step
+    n = min(wl.B, {5: 512, 3: 16, 4: 32, 2: 64}[args.config])    # images per step
     H, W, S = wl.H, wl.W, wl.S
     images = np.repeat(wl.images[:n], S, axis=0) if S > 1 else wl.images[:n]      # the reference's own formulation of S maps per image
     labels = wl.labels[:n].reshape(n * S, H, W)
@@ -412,8 +417,22 @@ def main():
 
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 
+    # A batch that fits the 126 MB L2 (config 2: 51 MB) is timed step by step with the L2 flushed in between (a 512 MB
+    # memset outside the timed pairs), as BASELINE.md section 3 asks; larger batches flush it by themselves.
+    flush_buf = torch.empty(512 << 20, dtype=torch.uint8, device=dev) if wl.step_bytes() < (200 << 20) else None
+
     def timed(fn, steps, after=lambda: None):
         sync()
+        if flush_buf is not None:
+            pairs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+            for a, b in pairs:
+                flush_buf.fill_(1)
+                a.record()
+                fn()
+                after()
+                b.record()
+            sync()
+            return max_over_ranks(sum(a.elapsed_time(b) for a, b in pairs))
         e0.record()
         for _ in range(steps):
             fn()
@@ -534,7 +553,9 @@ def main():
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "u8",
         "data": "synthetic",
         "config": {"workload": wl.name, "per_gpu_batch": B, "global_batch": wl.global_batch, "label_maps_per_image": S,
-                   "mean_segments_per_label_map": wl.Kmean, "l2": f"inputs ({mb:.0f} MB/step/GPU) exceed L2; no flush",
+                   "mean_segments_per_label_map": wl.Kmean,
+                   "l2": (f"inputs ({mb:.0f} MB/step/GPU) exceed L2; no flush" if flush_buf is None else
+                          f"inputs ({mb:.0f} MB/step/GPU) fit L2: every step timed on its own with a 512 MB memset before it"),
                    "parallelism": f"dp{world}: images sharded, rewards exchanged by {exchange}, EMA on the gathered vector" if world > 1 else "single GPU"},
         "e2e": {"value": e2e_value, "unit": "images/sec", "h2d_bytes_per_step": wl.step_bytes(),
                 "d2h_bytes_per_step": int(pr.numel() * 8), "ms_per_step": e2e_ms / e2e_steps, "steps": e2e_steps,
