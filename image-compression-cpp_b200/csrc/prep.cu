@@ -38,6 +38,7 @@ struct DivW {
 };
 
 // block-wide exclusive scan of one value per thread; returns the exclusive prefix, *total = the block's sum
+template <int PREP_W>
 __device__ __forceinline__ uint32_t block_exclusive(uint32_t mine, uint32_t* warp_tot, uint32_t* total) {
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     uint32_t inc = mine;
@@ -108,12 +109,14 @@ __device__ __forceinline__ void append_segment(const Tables& t, bool have, int c
     }
 }
 
-template <typename LT, bool VEC, bool CHG_SMEM>
-__global__ void __launch_bounds__(PREP_T, 4) prep_kernel(const LT* __restrict__ labels, Tables t, int cap_words, int ks_cap, int lists,
+// T threads per CTA: 256 (four CTAs per SM) when the batch fills the machine; 512 or 1024 when it has fewer maps than that
+// many CTAs, so that a map's latency-bound phases get more threads instead of leaving SMs idle
+template <typename LT, bool VEC, bool CHG_SMEM, int T>
+__global__ void __launch_bounds__(T, 1024 / T) prep_kernel(const LT* __restrict__ labels, Tables t, int cap_words, int ks_cap, int lists,
                                                        int L_min, RewardArgs rw) {
     extern __shared__ uint32_t smem[];
-    __shared__ long long red_lo[PREP_W], red_hi[PREP_W];
-    __shared__ uint32_t warp_tot[PREP_W];
+    __shared__ long long red_lo[(T / 32)], red_hi[(T / 32)];
+    __shared__ uint32_t warp_tot[(T / 32)];
     __shared__ long long s_min;
     __shared__ int s_bad, s_nbig;
 
@@ -137,9 +140,9 @@ __global__ void __launch_bounds__(PREP_T, 4) prep_kernel(const LT* __restrict__ 
         uint32_t* heads = t.heads + (int64_t)v * t.head_cap;
         uint32_t* hslot = t.hslot + (int64_t)v * t.head_cap;
 
-        for (int i = tid; i < cap_words; i += PREP_T) bitmap[i] = 0;
+        for (int i = tid; i < cap_words; i += T) bitmap[i] = 0;
         if (tid == 0) s_nbig = 0;
-        for (uint32_t g = ngroups + tid; g < nwords * 4u; g += PREP_T) chgb[g] = 0;     // padding bits of the last word
+        for (uint32_t g = ngroups + tid; g < nwords * 4u; g += T) chgb[g] = 0;     // padding bits of the last word
 
         // ---- mark: one bit per pixel, set at run heads
         if (VEC) {
@@ -148,16 +151,16 @@ __global__ void __launch_bounds__(PREP_T, 4) prep_kernel(const LT* __restrict__ 
             constexpr int NG = sizeof(LT) == 4 ? 2 : 1;
             LT cur[NG][8], nxt[NG][8], pv[NG], npv[NG];
             int x[NG];
-            const int stepx = (int)((PREP_T * NG * 8u) % (uint32_t)W);
+            const int stepx = (int)((T * NG * 8u) % (uint32_t)W);
 #pragma unroll
             for (int j = 0; j < NG; ++j) {
-                const uint32_t g = tid + j * PREP_T;
+                const uint32_t g = tid + j * T;
                 int y0;
                 divw(g * 8u, y0, x[j]);
                 npv[j] = 0;
                 if (g < ngroups) { load8<LT>(lab + g * 8u, nxt[j]); if (x[j]) npv[j] = __ldg(lab + g * 8u - 1); }
             }
-            for (uint32_t g0 = tid; g0 < ngroups; g0 += PREP_T * NG) {
+            for (uint32_t g0 = tid; g0 < ngroups; g0 += T * NG) {
                 bool rowstart[NG];
 #pragma unroll
                 for (int j = 0; j < NG; ++j) {
@@ -166,12 +169,12 @@ __global__ void __launch_bounds__(PREP_T, 4) prep_kernel(const LT* __restrict__ 
                     pv[j] = npv[j];
                     rowstart[j] = x[j] == 0;
                     x[j] += stepx; if (x[j] >= W) x[j] -= W;
-                    const uint32_t gn = g0 + (j + NG) * PREP_T;
+                    const uint32_t gn = g0 + (j + NG) * T;
                     if (gn < ngroups) { load8<LT>(lab + gn * 8u, nxt[j]); npv[j] = x[j] ? __ldg(lab + gn * 8u - 1) : (LT)0; }
                 }
 #pragma unroll
                 for (int j = 0; j < NG; ++j) {
-                    const uint32_t g = g0 + j * PREP_T;
+                    const uint32_t g = g0 + j * T;
                     if (g >= ngroups) break;
                     uint32_t m = (rowstart[j] || cur[j][0] != pv[j]) ? 1u : 0u;
 #pragma unroll
@@ -180,7 +183,7 @@ __global__ void __launch_bounds__(PREP_T, 4) prep_kernel(const LT* __restrict__ 
                 }
             }
         } else {
-            for (uint32_t g = tid; g < ngroups; g += PREP_T) {
+            for (uint32_t g = tid; g < ngroups; g += T) {
                 const uint32_t p0 = g * 8u;
                 int y, x;
                 divw(p0, y, x);
@@ -198,12 +201,12 @@ __global__ void __launch_bounds__(PREP_T, 4) prep_kernel(const LT* __restrict__ 
         __syncthreads();
 
         // ---- compact: the set bits as an ascending list of pixel indices
-        const uint32_t wpt = (nwords + PREP_T - 1) / PREP_T;
+        const uint32_t wpt = (nwords + T - 1) / T;
         const uint32_t w0 = min((uint32_t)tid * wpt, nwords), w1 = min(w0 + wpt, nwords);
         uint32_t mine = 0;
         for (uint32_t w = w0; w < w1; ++w) mine += __popc(chgw[w]);
         uint32_t nheads;
-        uint32_t hb = block_exclusive(mine, warp_tot, &nheads);
+        uint32_t hb = block_exclusive<T / 32>(mine, warp_tot, &nheads);
         const bool listed = nheads <= (uint32_t)t.head_cap;
         if (listed)
             for (uint32_t w = w0; w < w1; ++w) {
@@ -224,18 +227,18 @@ __global__ void __launch_bounds__(PREP_T, 4) prep_kernel(const LT* __restrict__ 
         if (listed) {
             // four heads per thread and trip: the positions, then the labels, are asked for together (two memory round trips
             // per trip instead of two per head)
-            for (uint32_t i0 = tid; i0 < nheads; i0 += 4 * PREP_T) {
+            for (uint32_t i0 = tid; i0 < nheads; i0 += 4 * T) {
                 uint32_t p[4];
                 LT l[4];
 #pragma unroll
-                for (int j = 0; j < 4; ++j) { const uint32_t i = i0 + j * PREP_T; p[j] = i < nheads ? heads[i] : 0xffffffffu; }
+                for (int j = 0; j < 4; ++j) { const uint32_t i = i0 + j * T; p[j] = i < nheads ? heads[i] : 0xffffffffu; }
 #pragma unroll
                 for (int j = 0; j < 4; ++j) l[j] = p[j] != 0xffffffffu ? __ldg(lab + p[j]) : (LT)0;
 #pragma unroll
-                for (int j = 0; j < 4; ++j) if (p[j] != 0xffffffffu) hslot[i0 + j * PREP_T] = mark(l[j]);
+                for (int j = 0; j < 4; ++j) if (p[j] != 0xffffffffu) hslot[i0 + j * T] = mark(l[j]);
             }
         } else {
-            for (uint32_t w = tid; w < nwords; w += PREP_T) {
+            for (uint32_t w = tid; w < nwords; w += T) {
                 uint32_t bits = chgw[w];
                 while (bits) { const int b = __ffs(bits) - 1; bits &= bits - 1; mark(__ldg(lab + w * 32u + b)); }
             }
@@ -248,7 +251,7 @@ __global__ void __launch_bounds__(PREP_T, 4) prep_kernel(const LT* __restrict__ 
         if (lane == 0) { red_lo[wid] = lo64; red_hi[wid] = hi64; }
         __syncthreads();
         if (tid == 0) {
-            for (int i = 1; i < PREP_W; ++i) { lo64 = min(lo64, red_lo[i]); hi64 = max(hi64, red_hi[i]); }
+            for (int i = 1; i < (T / 32); ++i) { lo64 = min(lo64, red_lo[i]); hi64 = max(hi64, red_hi[i]); }
             s_min = lo64;
             // the spread must fit the bitmap (unsigned arithmetic also covers overflow of hi-lo)
             s_bad = ((unsigned long long)hi64 - (unsigned long long)lo64 > (unsigned long long)cmask) ? ST_LABEL_RANGE : ST_OK;
@@ -258,7 +261,7 @@ __global__ void __launch_bounds__(PREP_T, 4) prep_kernel(const LT* __restrict__ 
         const uint32_t* chg_it = chgw;
         if (CHG_SMEM && !listed) {
             uint32_t* spill = heads;                                   // head_cap >= HW/8 words, the bitmap has HW/32
-            for (uint32_t w = tid; w < nwords; w += PREP_T) spill[w] = chgw[w];
+            for (uint32_t w = tid; w < nwords; w += T) spill[w] = chgw[w];
             chg_it = spill;
         }
         __syncthreads();
@@ -268,12 +271,12 @@ __global__ void __launch_bounds__(PREP_T, 4) prep_kernel(const LT* __restrict__ 
 
         if (!bad) {
             // ---- exclusive popcount scan over bitmap words: prefix[w] = set bits below word w
-            const int per = (cap_words + PREP_T - 1) / PREP_T;
+            const int per = (cap_words + T - 1) / T;
             const int b0 = min(tid * per, cap_words), b1 = min(b0 + per, cap_words);
             uint32_t cnt = 0;
             for (int w = b0; w < b1; ++w) cnt += __popc(bitmap[w]);
             uint32_t total;
-            uint32_t run = block_exclusive(cnt, warp_tot, &total);
+            uint32_t run = block_exclusive<T / 32>(cnt, warp_tot, &total);
             for (int w = b0; w < b1; ++w) { prefix[w] = run; run += __popc(bitmap[w]); }
             K = (int)total;
             if (K > t.Kmax) bad = ST_K_OVERFLOW;
@@ -288,7 +291,7 @@ __global__ void __launch_bounds__(PREP_T, 4) prep_kernel(const LT* __restrict__ 
             };
             // ---- keys: original label of each compact id, ascending
             long long* keys = t.keys + (int64_t)v * t.Kmax;
-            for (int w = tid; w < cap_words; w += PREP_T) {
+            for (int w = tid; w < cap_words; w += T) {
                 uint32_t bits = bitmap[w];
                 while (bits) {
                     const int b = __ffs(bits) - 1;
@@ -304,17 +307,17 @@ __global__ void __launch_bounds__(PREP_T, 4) prep_kernel(const LT* __restrict__ 
             const bool in_smem = K <= ks_cap;
             const StatsPtr st = in_smem ? StatsPtr{stab, stab + ks_cap, stab + 2 * ks_cap, stab + 3 * ks_cap, stab + 4 * ks_cap, 1}
                                         : StatsPtr{g_cnt, g_bb, g_bb + 1, g_bb + 2, g_bb + 3, 4};
-            for (int k = tid; k < K; k += PREP_T) {
+            for (int k = tid; k < K; k += T) {
                 const int kk = k * st.bst;
                 st.cnt[k] = 0; st.bx0[kk] = W; st.by0[kk] = H; st.bx1[kk] = -1; st.by1[kk] = -1;
             }
             __syncthreads();
             if (listed) {
-                for (uint32_t i0 = tid; i0 < nheads; i0 += 4 * PREP_T) {
+                for (uint32_t i0 = tid; i0 < nheads; i0 += 4 * T) {
                     uint32_t p[4], nx[4], sl[4];
 #pragma unroll
                     for (int j = 0; j < 4; ++j) {
-                        const uint32_t i = i0 + j * PREP_T;
+                        const uint32_t i = i0 + j * T;
                         p[j] = i < nheads ? heads[i] : 0xffffffffu;
                         nx[j] = i + 1 < nheads ? heads[i + 1] : HW;      // every row start is a head: the run ends in its row
                         sl[j] = i < nheads ? hslot[i] : 0u;
@@ -329,7 +332,7 @@ __global__ void __launch_bounds__(PREP_T, 4) prep_kernel(const LT* __restrict__ 
                     }
                 }
             } else {
-                for (uint32_t w = tid; w < nwords; w += PREP_T) {
+                for (uint32_t w = tid; w < nwords; w += T) {
                     uint32_t bits = chg_it[w];
                     while (bits) {
                         const int b = __ffs(bits) - 1;
@@ -351,7 +354,7 @@ __global__ void __launch_bounds__(PREP_T, 4) prep_kernel(const LT* __restrict__ 
             }
             __syncthreads();
             // ---- table rows out, and every segment into the work list of the kernel that takes it
-            for (int k0 = 0; k0 < K; k0 += PREP_T) {
+            for (int k0 = 0; k0 < K; k0 += T) {
                 const int k = k0 + tid;
                 const bool have = k < K;
                 int4 bb = make_int4(0, 0, -1, -1);
@@ -392,24 +395,33 @@ __global__ void __launch_bounds__(PREP_T, 4) prep_kernel(const LT* __restrict__ 
     }
 }
 
-template <typename LT, bool VEC, bool CHG_SMEM>
-static cudaError_t launch_t(const void* labels, const Tables& t, int lists, int L_min, const RewardArgs& rw, cudaStream_t st) {
+template <typename LT, bool VEC, bool CHG_SMEM, int T>
+static cudaError_t launch_tt(const void* labels, const Tables& t, int lists, int L_min, const RewardArgs& rw, cudaStream_t st) {
     const int cap_words = (int)(label_capacity(t.H, t.W) / 32);
     const int64_t nwords = chg_bytes(t.H, t.W) / 4;
     const int64_t un_words = CHG_SMEM ? (nwords > cap_words ? nwords : cap_words) : cap_words;
     const int ks_cap = t.Kmax < KS_SMEM ? t.Kmax : KS_SMEM;              // rows of the shared-memory stats table
     const size_t smem = ((size_t)cap_words + (size_t)un_words) * 4 + (size_t)ks_cap * 5 * 4;
-    auto k = prep_kernel<LT, VEC, CHG_SMEM>;
+    auto k = prep_kernel<LT, VEC, CHG_SMEM, T>;
     cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     int per = 0;
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, k, PREP_T, smem);
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, k, T, smem);
     if (e != cudaSuccess) return e;
     const int resident = sm_count() * (per < 1 ? 1 : per);
     const int grid = t.V < resident ? t.V : resident;                   // persistent beyond one wave: CTAs stride over the maps
-    k<<<grid, PREP_T, smem, st>>>(static_cast<const LT*>(labels), t, cap_words, ks_cap, lists, L_min, rw);
+    k<<<grid, T, smem, st>>>(static_cast<const LT*>(labels), t, cap_words, ks_cap, lists, L_min, rw);
     count_launch();
     return cudaGetLastError();
+}
+
+template <typename LT, bool VEC, bool CHG_SMEM>
+static cudaError_t launch_t(const void* labels, const Tables& t, int lists, int L_min, const RewardArgs& rw, cudaStream_t st) {
+    if (VEC && CHG_SMEM) {                      // the common case gets the wide CTAs for small batches
+        if (t.V <= sm_count()) return launch_tt<LT, VEC, CHG_SMEM, (VEC && CHG_SMEM) ? 1024 : PREP_T>(labels, t, lists, L_min, rw, st);
+        if (t.V <= 2 * sm_count()) return launch_tt<LT, VEC, CHG_SMEM, (VEC && CHG_SMEM) ? 512 : PREP_T>(labels, t, lists, L_min, rw, st);
+    }
+    return launch_tt<LT, VEC, CHG_SMEM, PREP_T>(labels, t, lists, L_min, rw, st);
 }
 
 template <typename LT>
