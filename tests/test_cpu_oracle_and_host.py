@@ -188,3 +188,20 @@ def test_exchange_classes_are_importable_without_a_gpu():
     """PipelinedGather / PeerGather need CUDA to construct; their module must still import on a CPU box."""
     from image_compression_cpp_b200 import sharding
     assert callable(sharding.PipelinedGather) and callable(sharding.PeerGather) and sharding.shard_range(10, 4, 3) == (8, 10)
+
+
+def test_bench_workload_sharding():
+    """bench.py's workload builder on CPU: strong scaling cuts the config's global batch into equal contiguous shards with
+    their own synthetic images, weak scaling keeps the per-GPU batch, and the algorithmic bytes follow BASELINE.md section 3."""
+    import bench
+    a = bench.Workload(2, 0, 2, "strong")
+    b = bench.Workload(2, 1, 2, "strong")
+    assert a.B == b.B == 32 and a.global_batch == 64
+    assert a.images.shape == (32, 3, 224, 224) and a.labels.shape == (32, 224, 224) and a.labels.dtype == np.int32
+    assert not np.array_equal(a.images[0], b.images[0])                       # rank 1 holds other images than rank 0
+    whole = bench.Workload(2, 0, 1, "strong")
+    assert whole.B == 64 and np.array_equal(whole.images[:32], a.images) and np.array_equal(whole.labels[32:], b.labels)
+    assert abs(whole.bytes_per_image() - (224 * 224 * 16 + whole.Kmean * 28 + 16)) < 1e-6
+    with pytest.raises(SystemExit):
+        bench.Workload(2, 0, 3, "strong")                                      # 64 images do not split over 3 GPUs
+    assert bench.CONFIGS[5]["G"] == 4096 and bench.CONFIGS[3]["H"] == 512 and bench.CONFIGS[4]["S"] == 8
