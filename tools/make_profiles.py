@@ -19,7 +19,7 @@ def last_json(path):
 
 
 def bench_lines(tag, pre):
-    for suffix, name in (("bench", "bench"), ("bench_weak", "bench_weak512"), ("bench_cfg3", "bench_cfg3"), ("bench_cfg4", "bench_cfg4"),
+    for suffix, name in (("bench", "bench"), ("bench_weak", "bench_weak512"), ("bench_cfg2", "bench_cfg2"), ("bench_cfg3", "bench_cfg3"), ("bench_cfg4", "bench_cfg4"),
                          ("bench_ref", "bench_reference_arm")):
         src = os.path.join(OUT, f"{pre}_{suffix}.json")
         if os.path.exists(src):
