@@ -1,3 +1,6 @@
+#!/usr/bin/env python
+"""Per-kernel device times of the reward path for batches of 8 .. 4096 config-5 images (inputs resident in HBM, CUDA events
+between the library's launches): separates the fixed cost of a launch from the per-image rate.  DESIGN.md section 6."""
 import ctypes as C, json, os, sys
 import numpy as np, torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
