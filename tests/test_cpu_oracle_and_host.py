@@ -117,6 +117,16 @@ def test_c_abi_argument_errors_without_a_gpu(icr):
                                            ctypes.c_float(0), ctypes.c_double(0), 1, None, None, None, None, None, None) == 1
     assert 4 * 64 * 36 < L.icr_workspace_bytes(4, 224, 224, 64) < 1 << 20        # no per-pixel plane in the workspace
     assert L.icr_label_capacity(224, 224) == 65536 and L.icr_label_capacity(512, 512) == 512 * 512
+    # the entry points added in round 2 refuse bad arguments before they touch a device
+    assert L.icr_estimate_png_size_segment_noalloc(None, 8, 8, 4, None, None, 0, 0, 0, 8, 8, 1, 4, ctypes.c_float(0), ctypes.c_float(0),
+                                                   ctypes.c_float(0), ctypes.c_double(0), 1, None, None, None, None, None, None) == 1
+    assert L.icr_compute_rewards_host_u8(None, 7, None, 0, None, 1, 1, 8, 8, ctypes.byref(p), None, None, None) == 1
+    assert b"image_layout" in L.icr_last_error()
+    assert L.icr_compute_rewards_host_u8(None, 0, None, 0, None, 1, 1, 8, 8, ctypes.byref(p), None, None, None) == 1
+    assert L.icr_pack_node_labels(None, None, 2, ctypes.c_int64(64), None, None) == 1
+    assert L.icr_exchange_rewards(None, None, 4, None, None, None) == 1
+    assert L.icr_nccl_comm_create(None, None, 2, 0) == 1 and L.icr_nccl_comm_ranks(None, None) == 1
+    assert L.icr_nccl_comm_destroy(None) == 0
     q = icr.IcrParams()
     L.icr_default_params(ctypes.byref(q))
     assert (q.min_pixels, q.L_min, q.adaptive_filter, q.lambda_) == (1, 4, 1, 0.5) and abs(q.overhead_base - 9.308622) < 1e-15
