@@ -43,6 +43,8 @@ static int cuda_fail(cudaError_t e, const char* what) {
 #define ICR_CUDA(x, what) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) return cuda_fail(e_, what); } while (0)
 
 static size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
+// Big segments are only shared out among CTAs when the grid holds at least two CTAs per segment: at most BIG_GRID_MAX / 2 slots
+static int merge_capacity(int) { return BIG_GRID_MAX / 2; }
 
 // Which estimator takes the warp-path work lists.  Both produce the same tables (the GPU suite runs under either);
 // ICR_ESTIMATOR=reg selects the register path of narrow.cu, anything else the shared-memory tile path of estimate.cu.
@@ -63,7 +65,7 @@ int sm_count() {
 }
 
 struct Layout { size_t K, status, counts, bboxes, keys, sizes, err, seg_prefix, sched, big_filter, clog2, heads, hslot, chg, slice_map_off,
-                nbig, done, list_a, list_b, list_big, total; };
+                nbig, done, big_merge, list_a, list_b, list_big, total; };
 
 static Layout layout(int V, int H, int W, int Kmax) {
     Layout l; size_t o = 0;
@@ -84,6 +86,7 @@ static Layout layout(int V, int H, int W, int Kmax) {
     l.slice_map_off = o; o = align_up(o + (size_t)V * 8);
     l.nbig = o; o = align_up(o + (size_t)V * 4);
     l.done = o; o = align_up(o + (size_t)V * 4);
+    l.big_merge = o; o = align_up(o + (size_t)merge_capacity(V) * sizeof(BigMerge));
     l.list_a = o; o = align_up(o + (size_t)V * Kmax * 8);
     l.list_b = o; o = align_up(o + (size_t)V * Kmax * 8);
     l.list_big = o; o = align_up(o + (size_t)V * Kmax * 8);
@@ -159,6 +162,7 @@ int icr_workspace_create(icr_workspace** out, int device, int V, int H, int W, i
     t.chg_global = chg_in_smem(H, W) ? nullptr : (uint8_t*)(ws->base + l.chg); t.chg_stride = chg_bytes(H, W);
     t.slice_map_off = (unsigned long long*)(ws->base + l.slice_map_off);
     t.nbig = (int32_t*)(ws->base + l.nbig); t.done = (int32_t*)(ws->base + l.done);
+    t.big_merge = (BigMerge*)(ws->base + l.big_merge); t.merge_cap = merge_capacity(V);
     t.list_a = (uint2*)(ws->base + l.list_a); t.list_b = (uint2*)(ws->base + l.list_b); t.list_big = (uint2*)(ws->base + l.list_big);
     t.list_cap = (int64_t)V * Kmax;
     std::vector<double> tab(CLOG2_N);
@@ -171,6 +175,7 @@ int icr_workspace_create(icr_workspace** out, int device, int V, int H, int W, i
     if (e == cudaSuccess) e = cudaMemset(ws->base + l.seg_prefix, 0, ((size_t)V + 1) * 4);
     if (e == cudaSuccess) e = cudaMemset(ws->base + l.sched, 0, (size_t)SCHED_N * 4);
     if (e == cudaSuccess) e = cudaMemset(ws->base + l.done, 0, (size_t)V * 4);
+    if (e == cudaSuccess) e = cudaMemset(ws->base + l.big_merge, 0, (size_t)merge_capacity(V) * sizeof(BigMerge));
     if (e != cudaSuccess) { cudaFree(ws->base); delete ws; return cuda_fail(e, "workspace init"); }
     *out = ws;
     return ICR_OK;

@@ -88,15 +88,36 @@ __device__ __forceinline__ double size_formula_big(double Hbar, unsigned long lo
     return (p.overhead + (double)h) + ((double)N * b_data) / 8.0;
 }
 
-// whole CTA cooperates on one segment; filt = >= h bytes of scratch (global)
-template <class Src>
-__device__ void block_segment(const Src& src, int x0, int y0, int w, int h, int C, const EstParams& p,
-                              uint8_t* filt, double* out, const BigDebug& dbg) {
-    __shared__ uint32_t s_hist[4 * 256];
-    __shared__ uint32_t s_tile[BIG_TILE_PX];
-    __shared__ double s_red[256];
-    __shared__ double s_Hc[4];
-    __shared__ unsigned long long s_ms, s_mc, s_mls;
+// shared memory of one CTA working on a big segment, declared once per kernel so that the code variants of block_segment
+// share it
+struct BigSmem {
+    uint32_t hist[4 * 256];
+    uint32_t tile[BIG_TILE_PX];         // residual words of a band / tile (chunks of more than one pixel)
+    uint32_t pix[BIG_TILE_PX];          // masked pixels of a band
+    uint32_t halo[BAND_MAX_W];          // the row above the band
+    double red[256];
+    double Hc[4];
+    unsigned long long ms, mc, mls;
+    uint32_t runs[8];
+    int ticket;
+    uint8_t filt[BAND_MAX_R];
+};
+
+// whole CTA cooperates on one segment; filt = >= h bytes of scratch (global).
+// part / nparts / mg: the bands of the banded path can be shared out among up to nparts CTAs (a batch with fewer big
+// segments than resident CTAs would otherwise leave most of the machine idle for the 270 us one CTA needs for a 224x224
+// bbox).  Every part adds its histogram and match statistics to the segment's merge slot; the part that arrives last reads
+// them back (clearing the slot) and finishes the segment.  Integer sums only, so the result does not depend on the split.
+// Returns true in the CTA that wrote *out.
+// SPLIT = false is the one-CTA code of before, compiled without any of the sharing (it is the path of large batches).
+template <class Src, bool SPLIT = false>
+__device__ bool block_segment(const Src& src, int x0, int y0, int w, int h, int C, const EstParams& p,
+                              uint8_t* filt, double* out, const BigDebug& dbg, BigSmem& sh, int part = 0, int nparts = 1, BigMerge* mg = nullptr) {
+    uint32_t* const s_hist = sh.hist;
+    uint32_t* const s_tile = sh.tile;
+    double* const s_red = sh.red;
+    double* const s_Hc = sh.Hc;
+    unsigned long long &s_ms = sh.ms, &s_mc = sh.mc, &s_mls = sh.mls;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
     for (int i = tid; i < 4 * 256; i += BIG_T) s_hist[i] = 0;
@@ -127,16 +148,27 @@ __device__ void block_segment(const Src& src, int x0, int y0, int w, int h, int 
             if (R >= l) R = (R / l) * l;
         }
     }
+    int parts = 1;                                             // CTAs that really share this segment
+    if (SPLIT) {
+        if (R > 0) parts = min(nparts, (h + R - 1) / R);
+        if (part >= parts) return false;                       // nothing left for this CTA (uniform over the CTA)
+    }
     if (R > 0) {
-        __shared__ uint32_t s_pix[BIG_TILE_PX];
-        __shared__ uint32_t s_halo[BAND_MAX_W];
-        __shared__ uint8_t s_filt[BAND_MAX_R];
+        int yb_begin = 0, yb_end = h;
+        if (SPLIT) {
+            const int nb = (h + R - 1) / R;
+            yb_begin = (int)((long long)part * nb / parts) * R;
+            yb_end = min(h, (int)((long long)(part + 1) * nb / parts) * R);
+        }
+        uint32_t* const s_pix = sh.pix;
+        uint32_t* const s_halo = sh.halo;
+        uint8_t* const s_filt = sh.filt;
         const uint32_t wpc = (uint32_t)(chunk >> 2);
         const bool quads = src.quads_ok();
         // Rule M for chunks of ONE pixel (every bbox of 49 153 .. 65 536 pixels, e.g. a 224x224 image): a chunk's runs follow from
         // which of its three byte pairs are equal, so {matched bytes, runs} of the eight cases sit in a table (low / high half
         // of a word) and the residual walk adds its pixel's entry on the spot: no second pass, no residual tile
-        __shared__ uint32_t s_runs[8];
+        uint32_t* const s_runs = sh.runs;
         if (tid < 8) {
             int run = 1, m = 0, n = 0;
             for (int c = 0; c < 3; ++c) {
@@ -146,11 +178,13 @@ __device__ void block_segment(const Src& src, int x0, int y0, int w, int h, int 
             if (run >= p.L_min) { m += run; ++n; }
             s_runs[tid] = (uint32_t)m | (uint32_t)n << 16;
         }
-        for (int yb = 0; yb < h; yb += R) {
+        for (int yb = yb_begin; yb < yb_end; yb += R) {
             const int nr = min(R, h - yb);
             const int here = nr * w;
-            // the row above the band: zeros above the bbox, else the last row of the band before (always a full band)
-            for (int x = tid; x < w; x += BIG_T) s_halo[x] = yb ? s_pix[(R - 1) * w + x] : 0u;
+            // the row above the band: zeros above the bbox, else the last row of the band before (always a full band), which
+            // the first band of a later part fetches itself
+            if (SPLIT && yb == yb_begin && yb > 0) { for (int x = tid; x < w; x += BIG_T) s_halo[x] = src.px(y0 + yb - 1, x0 + x); }
+            else { for (int x = tid; x < w; x += BIG_T) s_halo[x] = yb ? s_pix[(R - 1) * w + x] : 0u; }
             __syncthreads();
             // a warp per row, lanes along x (these bboxes are wide: no row/column split per pixel)
             for (int r = warp; r < nr; r += BIG_T / 32) {
@@ -388,6 +422,20 @@ __device__ void block_segment(const Src& src, int x0, int y0, int w, int h, int 
     if (ms) { atomicAdd(&s_ms, ms); atomicAdd(&s_mls, ms); }    // match_symbols == match_len_sum (:440-442)
     if (mc) atomicAdd(&s_mc, mc);
     __syncthreads();
+    if (SPLIT && parts > 1) {
+        int& s_ticket = sh.ticket;
+        for (int i = tid; i < 4 * 256; i += BIG_T) { const uint32_t u = s_hist[i]; if (u) atomicAdd(&mg->hist[i], u); }
+        if (tid == 0) { if (s_ms) atomicAdd(&mg->ms, s_ms); if (s_mc) atomicAdd(&mg->mc, s_mc); }
+        __threadfence();
+        __syncthreads();
+        if (tid == 0) s_ticket = (int)atomicAdd(&mg->done, 1u);
+        __syncthreads();
+        if (s_ticket != parts - 1) return false;               // another part will finish the segment
+        __threadfence();
+        for (int i = tid; i < 4 * 256; i += BIG_T) s_hist[i] = atomicExch(&mg->hist[i], 0u);     // read past L1 and leave the slot clear
+        if (tid == 0) { s_ms = atomicExch(&mg->ms, 0ull); s_mls = s_ms; s_mc = atomicExch(&mg->mc, 0ull); mg->done = 0u; }
+        __syncthreads();
+    }
 
     // ---- entropy per channel with the reference's 256-leaf tree (:281-309)
     const uint32_t n = (uint32_t)((unsigned long long)w * (unsigned long long)h);
@@ -412,18 +460,26 @@ __device__ void block_segment(const Src& src, int x0, int y0, int w, int h, int 
         if (dbg.match) { dbg.match[0] = s_ms; dbg.match[1] = s_mc; dbg.match[2] = s_mls; }
     }
     __syncthreads();
+    return true;
 }
 
 // Persistent CTAs pull the segments prep put on list_big (Rule M can fire, or the bbox is wider or larger than the
 // register path takes), one segment per CTA at a time.  This is always the last kernel of a batch call: whichever
 // CTA finishes last resets the work lists for the next call and, in a sharded run, tells the peers that this rank's
 // rewards have landed.
-template <typename LT>
+// SPLIT: the launch has so few label maps that big segments may be shared out among CTAs (decided here from the list's
+// length); large batches run the kernel compiled without that code.
+template <typename LT, bool SPLIT>
 __global__ void __launch_bounds__(BIG_T, 4) big_kernel(Tables t, Inputs in, EstParams p, RewardArgs rw) {
     __shared__ int s_next, s_last;
+    __shared__ BigSmem sh;
     const int64_t HW = (int64_t)t.H * t.W;
     BigDebug none{};
     const int total = t.sched[SC_N_BIG];
+    // fewer big segments than half the grid: P CTAs per segment (work item = segment * P + part)
+    int P = 1;
+    if (SPLIT && total > 0 && total <= t.merge_cap) P = max(1, min((int)gridDim.x / total, BIG_MAX_PARTS));
+    const int items = total * P;
     uint8_t* filt = t.big_filter + (int64_t)blockIdx.x * t.H;
     // Rule W for the maps whose sizes all came from the kernel before: a warp per map
     for (int v = blockIdx.x * (BIG_T / 32) + (threadIdx.x >> 5); v < t.V; v += gridDim.x * (BIG_T / 32))
@@ -431,18 +487,17 @@ __global__ void __launch_bounds__(BIG_T, 4) big_kernel(Tables t, Inputs in, EstP
     for (;;) {
         if (threadIdx.x == 0) s_next = total > 0 ? atomicAdd(&t.sched[SC_CUR_BIG], 1) : 0;
         __syncthreads();
-        const int i = s_next;
-        if (i >= total) break;
+        if (s_next >= items) break;
+        const int i = s_next / P, part = s_next - i * P;
         const uint2 e = t.list_big[i];
         const int v = (int)e.x, k = (int)e.y;
         const int64_t row = (int64_t)v * t.Kmax + k;
         const int4 bb = t.bboxes[row];
         SrcPlanar<LT> src(in.images + (int64_t)(v / in.S) * 3 * HW, static_cast<const LT*>(in.labels) + (int64_t)v * HW, HW, t.W,
                           (LT)t.keys[row]);
-        block_segment(src, bb.x, bb.y, bb.z - bb.x + 1, bb.w - bb.y + 1, 4, p, filt, t.seg_sizes + row, none);
-        if (threadIdx.x == 0) {                           // the thread that stored the size
-            s_last = segment_done(t, v, t.nbig[v]);
-        }
+        const bool wrote = block_segment<SrcPlanar<LT>, SPLIT>(src, bb.x, bb.y, bb.z - bb.x + 1, bb.w - bb.y + 1, 4, p, filt, t.seg_sizes + row,
+                                                               none, sh, part, P, SPLIT ? t.big_merge + i : nullptr);
+        if (threadIdx.x == 0) s_last = wrote ? segment_done(t, v, t.nbig[v]) : 0;     // the thread that stored the size
         __syncthreads();
         if (s_last && threadIdx.x < 32) {                 // every size of this map is final: Rule W
             __threadfence();
@@ -473,19 +528,28 @@ __global__ void __launch_bounds__(BIG_T) big_debug_kernel(Tables t, Inputs in, E
     const int64_t HW = (int64_t)t.H * t.W;
     SrcPlanar<LT> src(in.images + (int64_t)(v / in.S) * 3 * HW, static_cast<const LT*>(in.labels) + (int64_t)v * HW, HW, t.W,
                       (LT)t.keys[(int64_t)v * t.Kmax + k]);
-    block_segment(src, bb.x, bb.y, bb.z - bb.x + 1, bb.w - bb.y + 1, 4, p, t.big_filter, &scratch, dbg);
+    __shared__ BigSmem sh;
+    block_segment(src, bb.x, bb.y, bb.z - bb.x + 1, bb.w - bb.y + 1, 4, p, t.big_filter, &scratch, dbg, sh);
 }
 
 __global__ void __launch_bounds__(BIG_T) single_segment_kernel(SrcRaw src, int x0, int y0, int w, int h, EstParams p,
                                                                 uint8_t* filt, double* out, BigDebug dbg) {
-    block_segment(src, x0, y0, w, h, src.C, p, filt, out, dbg);
+    __shared__ BigSmem sh;
+    block_segment(src, x0, y0, w, h, src.C, p, filt, out, dbg, sh);
 }
 
 cudaError_t launch_big(const Tables& t, const Inputs& in, const EstParams& p, const RewardArgs& rw, cudaStream_t st) {
     int grid = sm_count() * 4;
     if (grid > BIG_GRID_MAX) grid = BIG_GRID_MAX;
-    if (in.label_dtype == ICR_LABELS_I64) big_kernel<int64_t><<<grid, BIG_T, 0, st>>>(t, in, p, rw);
-    else big_kernel<int32_t><<<grid, BIG_T, 0, st>>>(t, in, p, rw);
+    // a big segment can only get a second CTA when the grid holds two per segment, and every map may bring one
+    const bool split = 2 * t.V <= grid;
+    if (in.label_dtype == ICR_LABELS_I64) {
+        if (split) big_kernel<int64_t, true><<<grid, BIG_T, 0, st>>>(t, in, p, rw);
+        else big_kernel<int64_t, false><<<grid, BIG_T, 0, st>>>(t, in, p, rw);
+    } else {
+        if (split) big_kernel<int32_t, true><<<grid, BIG_T, 0, st>>>(t, in, p, rw);
+        else big_kernel<int32_t, false><<<grid, BIG_T, 0, st>>>(t, in, p, rw);
+    }
     count_launch();
     return cudaGetLastError();
 }

@@ -22,6 +22,11 @@ enum : int { ST_OK = 0, ST_LABEL_RANGE = 1, ST_K_OVERFLOW = 2 };
 constexpr int KS_SMEM = 2048;          // per-CTA shared-memory stats table entries in prep
 constexpr int64_t LCAP_MAX = 1 << 19;  // label bitmap capacity (bits) that fits shared memory
 
+// Merge slot of a big segment whose bands are shared out among several CTAs (big_segment.cu): the parts add their
+// histograms and match statistics here, the part that finishes last reads them back, clears the slot and computes the size.
+struct BigMerge { uint32_t hist[4 * 256]; unsigned long long ms, mc; uint32_t done, pad[3]; };
+constexpr int BIG_MAX_PARTS = 16;      // most CTAs that share one big segment
+
 struct Tables {            // device pointers into the workspace, V label maps
     int32_t* K;            // [V]
     int32_t* status;       // [V]
@@ -50,6 +55,8 @@ struct Tables {            // device pointers into the workspace, V label maps
     int64_t list_cap;
     int32_t* nbig;         // [V] segments of a map on list_big (prep)
     int32_t* done;         // [V] big-kernel segments of a map whose size has been written; the writer of the last one computes Rule W
+    BigMerge* big_merge;   // [merge_cap] all zero between batch calls
+    int merge_cap;
     unsigned long long* slice_map_off;   // [V] byte offset of a map's first slice in the packed slice buffer (slices.cu)
     const double* clog2;   // [CLOG2_N] c*log2(c)
     // multi-GPU gather fused into the reward writer (icr_compute_rewards_gather): the reward of map v also goes to

@@ -162,3 +162,30 @@ def test_seeded_fuzz_slice(icr, orc, dev):
     cases, worst = fuzz_parity.run(10000, seed=20261105, budget_s=25.0, log=lambda *a: None)
     assert cases >= 20, f"only {cases} fuzz cases fitted the time box"
     assert worst < 1e-9
+
+
+def test_big_segments_shared_among_ctas_give_the_same_sizes(icr, orc, dev):
+    """A batch with fewer big segments than half the grid shares each of them out among several CTAs (bands of rows, merged
+    through integer atomics); a large batch gives every big segment one CTA.  Same maps, both ways: sizes and rewards bit
+    for bit, and both against the oracle.  One whole-image segment per map plus maps with a background around rectangles."""
+    H, W = 224, 224
+    images, labels, sizes = synth.make_batch(5, B=8, seed0=7300)
+    labels = labels.copy()
+    labels[:4] = 9                                                        # whole-image segments (Rule M, one-pixel chunks)
+    for b in range(4, 8):                                                 # rectangles on a border-touching background
+        labels[b][0, :], labels[b][-1, :], labels[b][:, 0], labels[b][:, -1] = -5, -5, -5, -5
+    want = _oracle_all(orc, images, labels, sizes, Kstride=256)
+    small = icr.Workspace(dev, 8, H, W, 256)
+    ti, tl, ts = (torch.from_numpy(a).to(dev) for a in (images, labels, sizes))
+    got_small = icr.compute_rewards_batched(ti, tl, ts, workspace=small).cpu().numpy()
+    tab_small = [t.cpu().numpy() for t in small.tables()]
+    _compare(got_small, tab_small, want, n_tables=8)
+    reps = 40                                                             # 320 maps: more than half the grid, one CTA per big segment
+    large = icr.Workspace(dev, 8 * reps, H, W, 256)
+    got_large = icr.compute_rewards_batched(ti.repeat(reps, 1, 1, 1), tl.repeat(reps, 1, 1), ts.repeat(reps), workspace=large).cpu().numpy()
+    tab_large = [t.cpu().numpy() for t in large.tables()]
+    assert np.array_equal(got_large[:8], got_small) and np.array_equal(got_large[-8:], got_small)
+    assert np.array_equal(tab_large[3][:8], tab_small[3], equal_nan=True)  # segment sizes
+    # and again on the small workspace: the merge slots were left clear
+    again = icr.compute_rewards_batched(ti, tl, ts, workspace=small).cpu().numpy()
+    assert np.array_equal(again, got_small)

@@ -7,7 +7,14 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from image_compression_cpp_b200 import reward, synth
 dev = torch.device("cuda:0"); L = reward.lib()
 im, lab, sz = synth.make_batch(5, B=64)
-for B in (8, 64, 128, 256, 512, 1024, 2048, 4096):
+if "bg" in sys.argv[1:]:          # a third of each map's rectangles melted into a border-touching background (one big segment per map)
+    lab = lab.copy()
+    for b in range(lab.shape[0]):
+        ids = np.unique(lab[b])
+        bg = np.random.default_rng(b).choice(ids, size=len(ids) // 3, replace=False)
+        lab[b][np.isin(lab[b], bg)] = -5
+        lab[b][0, :], lab[b][-1, :], lab[b][:, 0], lab[b][:, -1] = -5, -5, -5, -5
+for B in ((8, 64, 128, 256, 512, 1024) if "bg" in sys.argv[1:] else (8, 64, 128, 256, 512, 1024, 2048, 4096)):
     reps = -(-B // 64)
     ti = torch.from_numpy(np.tile(im, (reps, 1, 1, 1))[:B]).to(dev); tl = torch.from_numpy(np.tile(lab, (reps, 1, 1))[:B]).to(dev); ts = torch.from_numpy(np.tile(sz, reps)[:B]).to(dev)
     ws = reward.Workspace(dev, B, 224, 224, Kmax=1024); prm = reward.make_params(); out = torch.empty(B, dtype=torch.float64, device=dev)
