@@ -1,9 +1,11 @@
-// big-segment path: one CTA per segment, any size, any channel count 1..4.
+// big-segment path: one CTA per segment (several CTAs per segment when a small batch has fewer segments than the grid has
+// CTAs: SPLIT), any size, any channel count 1..4.
 // Used (a) by the batch for the few segments large enough for Rule M match statistics
 // (chunk = ceil(N/65536) >= L_min, src/png_size_estimator.cu:416-451), and (b) as the
 // pointer-level drop-in for estimate_png_size_masked_segment_to_output (:472-591).
 // Banded path (RGBA, chunks of whole pixels, bbox up to BAND_MAX_W wide): a band of rows is fetched once into shared
-// memory and serves the filter choice, the residuals + histogram and the run statistics of the band.
+// memory (aligned quads) and serves the filter choice, the residuals + histogram and the run statistics of the band; chunks
+// of one pixel take their run statistics from an 8-entry table inside the residual walk.
 // General path: phase 1, a warp per bbox row, lanes along x, packed-byte costs, arg-min -> filter id per row;
 // phase 2, the filtered stream goes through shared memory a tile at a time: a lane per pixel computes the residual
 // bytes and feeds the histogram, then a thread per reference chunk walks its bytes for the run statistics.
