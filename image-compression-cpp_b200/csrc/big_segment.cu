@@ -475,6 +475,7 @@ template <typename LT, bool SPLIT>
 __global__ void __launch_bounds__(BIG_T, 4) big_kernel(Tables t, Inputs in, EstParams p, RewardArgs rw) {
     __shared__ int s_next, s_last;
     __shared__ BigSmem sh;
+    ICR_GRID_DEP_WAIT();                  // every segment size of the estimator is final
     const int64_t HW = (int64_t)t.H * t.W;
     BigDebug none{};
     const int total = t.sched[SC_N_BIG];
@@ -546,11 +547,11 @@ cudaError_t launch_big(const Tables& t, const Inputs& in, const EstParams& p, co
     // a big segment can only get a second CTA when the grid holds two per segment, and every map may bring one
     const bool split = 2 * t.V <= grid;
     if (in.label_dtype == ICR_LABELS_I64) {
-        if (split) big_kernel<int64_t, true><<<grid, BIG_T, 0, st>>>(t, in, p, rw);
-        else big_kernel<int64_t, false><<<grid, BIG_T, 0, st>>>(t, in, p, rw);
+        if (split) launch_dependent(big_kernel<int64_t, true>, dim3(grid), dim3(BIG_T), 0, st, t, in, p, rw);
+        else launch_dependent(big_kernel<int64_t, false>, dim3(grid), dim3(BIG_T), 0, st, t, in, p, rw);
     } else {
-        if (split) big_kernel<int32_t, true><<<grid, BIG_T, 0, st>>>(t, in, p, rw);
-        else big_kernel<int32_t, false><<<grid, BIG_T, 0, st>>>(t, in, p, rw);
+        if (split) launch_dependent(big_kernel<int32_t, true>, dim3(grid), dim3(BIG_T), 0, st, t, in, p, rw);
+        else launch_dependent(big_kernel<int32_t, false>, dim3(grid), dim3(BIG_T), 0, st, t, in, p, rw);
     }
     count_launch();
     return cudaGetLastError();

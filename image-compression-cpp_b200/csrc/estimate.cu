@@ -442,6 +442,8 @@ __global__ void __launch_bounds__(EST_WARPS * 32, 4) estimate_kernel(Tables t, I
     WarpSmem& sm = wsm[warp];
     for (int i = lane; i < 1024; i += 32) sm.hist[i] = 0;
     __syncwarp();
+    ICR_GRID_DEP_LAUNCH();                // the tail kernel's CTAs may take the places of this kernel's CTAs as they leave
+    ICR_GRID_DEP_WAIT();                  // prep's tables and lists are complete
     const int64_t HW = (int64_t)t.H * t.W;
     // the four work lists back to back (prep fills only the first for this kernel; by width class for narrow.cu):
     // list_a front, list_b front, list_b back, list_a back
@@ -508,7 +510,8 @@ static cudaError_t launch_est_t(const Tables& t, const Inputs& in, const EstPara
         if (per < 1) per = 1;
         if (dev >= 0 && dev < 16) per_sm[dev] = per;
     }
-    kern<<<sm_count() * per, EST_WARPS * 32, smem, st>>>(t, in, p, rw);     // persistent: warps pull work until the list is empty
+    e = launch_dependent(kern, dim3(sm_count() * per), dim3(EST_WARPS * 32), smem, st, t, in, p, rw);     // persistent: warps pull work until the list is empty
+    if (e != cudaSuccess) return e;
     count_launch();
     return cudaGetLastError();
 }

@@ -7,6 +7,36 @@
 // Bounds checks of our own (compute-sanitizer is not available on the GPU pool): a build with -DICR_CHECKED asserts every
 // index into the shared-memory tables and the workspace lists (tools/build_variants.sh all:checked:-DICR_CHECKED, then
 // ICR_LIB=tools/_variants/libicr_checked.so python -m pytest tests -m gpu).  A failed check aborts the kernel with file:line.
+// Programmatic dependent launch (-DICR_PDL=0 turns it off): a kernel lets the next one of the call start its CTAs while its
+// own last ones still run; the next one sets up its shared memory and then waits for the whole predecessor before it reads
+// what that wrote.  4-6 us per call: 43 -> 37 us for a batch of 8 images, 228 -> 223 us for 512.
+#ifndef ICR_PDL
+#define ICR_PDL 1
+#endif
+#if ICR_PDL
+#define ICR_GRID_DEP_WAIT() asm volatile("griddepcontrol.wait;" ::: "memory")
+#define ICR_GRID_DEP_LAUNCH() asm volatile("griddepcontrol.launch_dependents;" ::: "memory")
+#else
+#define ICR_GRID_DEP_WAIT() ((void)0)
+#define ICR_GRID_DEP_LAUNCH() ((void)0)
+#endif
+// launch `kern` as a programmatic dependent of the kernel before it in the stream (plain launch without ICR_PDL)
+template <typename... KArgs, typename... Args>
+static inline cudaError_t launch_dependent(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
+#if ICR_PDL
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
+#else
+    kern<<<grid, block, smem, st>>>(args...);
+    return cudaSuccess;
+#endif
+}
+
 #ifdef ICR_CHECKED
 #include <cassert>
 #define ICR_DCHECK(c) assert(c)

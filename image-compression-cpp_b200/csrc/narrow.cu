@@ -440,6 +440,8 @@ __global__ void __launch_bounds__(NRW_WARPS * 32, NRW_MIN_CTAS) narrow_kernel(Ta
     uint32_t* hist = s_hist[warp];
     for (int i = lane; i < 1024; i += 32) hist[i] = 0;
     __syncwarp();
+    ICR_GRID_DEP_LAUNCH();                // the tail kernel's CTAs may take the places of this kernel's CTAs as they leave
+    ICR_GRID_DEP_WAIT();                  // prep's tables and lists are complete
     const uint32_t HW = (uint32_t)t.H * (uint32_t)t.W;
     // the four work lists back to back, widest bboxes first: list_a front, list_b front, list_b back, list_a back
     const int e0 = t.sched[SC_N_W128], e1 = e0 + t.sched[SC_N_W64], e2 = e1 + t.sched[SC_N_W32], total = e2 + t.sched[SC_N_W16];
@@ -506,7 +508,8 @@ static cudaError_t launch_narrow_t(const Tables& t, const Inputs& in, const EstP
         if (per < 1) per = 1;
         if (dev >= 0 && dev < 16) per_sm[dev] = per;
     }
-    kern<<<sm_count() * per, NRW_WARPS * 32, 0, st>>>(t, in, p, rw);       // persistent: warps pull segments until the list is empty
+    const cudaError_t le = launch_dependent(kern, dim3(sm_count() * per), dim3(NRW_WARPS * 32), 0, st, t, in, p, rw);   // persistent: warps pull segments until the list is empty
+    if (le != cudaSuccess) return le;
     count_launch();
     return cudaGetLastError();
 }

@@ -120,6 +120,7 @@ __global__ void __launch_bounds__(T, 1024 / T) prep_kernel(const LT* __restrict_
     __shared__ long long s_min;
     __shared__ int s_bad, s_nbig;
 
+    ICR_GRID_DEP_LAUNCH();                // the estimator's CTAs may take the places of this kernel's CTAs as they leave
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int H = t.H, W = t.W;
     const uint32_t HW = (uint32_t)H * (uint32_t)W;                       // below 2^31 (icr_workspace_create)
