@@ -43,8 +43,9 @@ static int cuda_fail(cudaError_t e, const char* what) {
 #define ICR_CUDA(x, what) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) return cuda_fail(e_, what); } while (0)
 
 static size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
-// Big segments are only shared out among CTAs when the grid holds at least two CTAs per segment: at most BIG_GRID_MAX / 2 slots
-static int merge_capacity(int) { return BIG_GRID_MAX / 2; }
+// Big segments are only shared out among CTAs when the grid holds at least two CTAs per segment (at most BIG_GRID_MAX / 2
+// of them); four slots per label map cover a background and a few more (a batch with more big segments runs them one CTA each)
+static int merge_capacity(int V) { return 4 * (int64_t)V < BIG_GRID_MAX / 2 ? 4 * V : BIG_GRID_MAX / 2; }
 
 // Which estimator takes the warp-path work lists.  Both produce the same tables (the GPU suite runs under either);
 // ICR_ESTIMATOR=reg selects the register path of narrow.cu, anything else the shared-memory tile path of estimate.cu.
